@@ -1,0 +1,131 @@
+/*
+ * pq_b200.h - C ABI of libpq_b200.so: the B200 (sm_100a) product-quantization
+ * linear kernels.  This is the drop-in boundary for the reference's native PQ
+ * (AQLM) ops.  Plain pointers and sizes only; no torch types; no allocation and
+ * no synchronisation inside, so every call is CUDA-graph capturable.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference):
+ *   pq_b200_dequant  <- aqlm_dequant   csrc/ops.h:129-131, csrc/torch_bindings.cpp:169-173,
+ *                                      csrc/quantization/aqlm/gemm_kernels.cu:544-597
+ *   pq_b200_gemm     <- aqlm_gemm      csrc/ops.h:123-127, csrc/torch_bindings.cpp:163-167,
+ *                                      csrc/quantization/aqlm/gemm_kernels.cu:519-542
+ *                       and, for tokens > 6, optimized_dequantize_gemm
+ *                       (vllm/model_executor/layers/quantization/aqlm.py:132-156)
+ *   pq_b200_allreduce_* <- CustomAllreduce  csrc/custom_all_reduce.cuh:214-506
+ *
+ * Tensor layouts are the reference checkpoint layouts (aqlm.py:253-316):
+ *   codes      [n, k/d, m]      int8 (nbits <= 8) or int16 (nbits <= 16), signed storage,
+ *                               index = (unsigned)code mod 2^nbits      (aqlm.py:32-34)
+ *   codebooks  [n_parts*m, 2^nbits, 1, d]  fp16 / bf16
+ *   scales     [n] (checkpoint shape [n,1,1,1])  fp16 / bf16
+ *   x          [t, k] row stride x_stride elements;  y [t, n] row stride y_stride
+ * Partition p owns rows [sum(part_sizes[:p]), +part_sizes[p]) and codebooks
+ * [p*m, (p+1)*m)                                               (aqlm.py:110-126).
+ *
+ * Every function returns 0 on success, a negative PQ_ERR_* on a bad argument,
+ * or a positive cudaError_t from the launch.
+ */
+#ifndef PQ_B200_H_
+#define PQ_B200_H_
+
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define PQ_API __attribute__((visibility("default")))
+#else
+#define PQ_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PQ_B200_ABI_VERSION 1
+#define PQ_MAX_PARTS 8
+
+enum { PQ_F16 = 0, PQ_BF16 = 1 };
+
+enum {
+  PQ_OK = 0,
+  PQ_ERR_DTYPE = -1,       /* dtype not PQ_F16 / PQ_BF16 */
+  PQ_ERR_FORMAT = -2,      /* (nbits, d, m) outside the supported grid */
+  PQ_ERR_SHAPE = -3,       /* k % d != 0, sizes <= 0, partition sizes do not sum to n */
+  PQ_ERR_ALIGN = -4,       /* a pointer or stride is not aligned as documented */
+  PQ_ERR_WORKSPACE = -5,   /* workspace too small (see pq_b200_workspace_bytes) */
+  PQ_ERR_NULL = -6,        /* required pointer is NULL */
+  PQ_ERR_UNSUPPORTED = -7, /* valid request this build has no kernel for */
+  PQ_ERR_DEVICE = -8       /* not an sm_100 device */
+};
+
+/* which kernel family pq_b200_gemm uses */
+enum {
+  PQ_ALGO_AUTO = 0,
+  PQ_ALGO_GEMV_DIRECT = 1, /* codebook gather in shared memory / L2, CUDA cores            */
+  PQ_ALGO_GEMV_LUT = 2,    /* per-token x.centroid lookup tables (nbits <= 8)               */
+  PQ_ALGO_GEMM_TC = 3      /* dequant tile -> smem -> tcgen05.mma, TMEM accumulator         */
+};
+
+PQ_API int pq_b200_abi_version(void);
+/* Launch decode kernels with programmatic dependent launch (off by default). */
+PQ_API void pq_b200_set_pdl(int enabled);
+PQ_API const char* pq_b200_strerror(int code);
+
+/* Unscaled (scales == NULL; what aqlm_dequant returns, gemm_kernels.cu:563-592) or
+ * scaled (aqlm.py:70-72) weights w_out[n, k].  Sum over the m codebooks is
+ * accumulated in fp32 in codebook order and rounded to nearest even once; the
+ * scale multiply rounds once more.  Bit-exact against aqlm.py:37-74.
+ * Alignment: codebooks, w_out 16 bytes. */
+PQ_API int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales,
+                    void* w_out, int64_t n, int64_t k, int d, int nbits, int m,
+                    const int64_t* part_sizes, int n_parts, int dtype, void* stream);
+
+/* Workspace (bytes) pq_b200_gemm needs for this problem with `algo`. */
+PQ_API int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d,
+                                int nbits, int m, int n_parts);
+
+/* y[t, n] = x[t, k] . W^T * scales + bias, W as in pq_b200_dequant.
+ * bias may be NULL.  workspace may be NULL when pq_b200_workspace_bytes() == 0.
+ * algo: PQ_ALGO_AUTO picks by (t, format).  Accumulation is fp32; scale and bias
+ * are applied in fp32 before the single rounding of y.
+ * Alignment: x, y, codebooks 16 bytes; x_stride, y_stride in elements. */
+PQ_API int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                 const void* scales, const void* bias, void* y, int64_t y_stride,
+                 int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                 const int64_t* part_sizes, int n_parts, int dtype, int algo,
+                 void* workspace, int64_t workspace_bytes, void* stream);
+
+/* Which PQ_ALGO_* would PQ_ALGO_AUTO choose. */
+PQ_API int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+
+/* ---- tensor-parallel reduction hook (row-parallel O / down projections) -------------
+ * One-shot all-reduce over peer-mapped buffers (NVLink P2P).  The caller (host side,
+ * vllm_pq_b200/distributed.py) allocates one staging buffer and one flag buffer per rank
+ * with pq_b200_malloc, exchanges CUDA IPC handles and passes the world's mapped pointers:
+ *   peer_data[r]  : rank r's staging buffer, 2 * world * slot_bytes bytes
+ *   peer_flags[r] : rank r's flag buffer, PQ_AR_FLAG_BYTES bytes, zeroed once at start
+ * n_elems * 2 <= slot_bytes; n_elems * 2 a multiple of 16; world in {2, 4, 8}.
+ * Replaces cross_device_reduce_1stage (custom_all_reduce.cuh:214-230) plus the staging
+ * memcpy of custom_all_reduce.cu:75-77: the kernel pushes the input straight into every
+ * peer's buffer. The epoch counter lives in the flag buffer and is advanced on the device,
+ * so a launch is CUDA-graph replayable. Sum order is rank 0..world-1 in fp32 on every
+ * rank: results are bitwise identical across ranks (custom_all_reduce.cuh:204-212). */
+#define PQ_AR_FLAG_BYTES 4096
+#define PQ_AR_MAX_WORLD 8
+PQ_API int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems, int dtype,
+                                     void* const* peer_data, void* const* peer_flags,
+                                     int rank, int world, int64_t slot_bytes, void* stream);
+
+/* Device buffers whose base address is what cudaIpcGetMemHandle maps (torch's caching
+ * allocator sub-allocates, so its pointers cannot be shared this way), and the 64-byte
+ * cudaIpcMemHandle_t exchange (reference: custom_all_reduce.py:178-201). */
+PQ_API int pq_b200_malloc(int64_t bytes, void** out);
+PQ_API int pq_b200_free(void* p);
+PQ_API int pq_b200_memset_async(void* p, int value, int64_t bytes, void* stream);
+PQ_API int pq_b200_ipc_get_handle(void* ptr, void* handle64);
+PQ_API int pq_b200_ipc_open_handle(void* handle64, void** out);
+PQ_API int pq_b200_ipc_close_handle(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PQ_B200_H_ */

@@ -1,0 +1,154 @@
+"""Host-side logic, no GPU: the C-ABI library loads and exports what include/pq_b200.h declares,
+the plugin API mirrors the reference's, and the product never routes through the oracle."""
+import ctypes
+import os
+import re
+
+import pytest
+import torch
+
+import vllm_pq_b200 as P
+from oracle import ref_loader
+from vllm_pq_b200 import _lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "pq_b200.h")).read()
+    return sorted(set(re.findall(r"PQ_API\s+[\w\s\*]+?\b(pq_b200_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    syms = header_symbols()
+    assert len(syms) >= 14
+    for s in syms:
+        assert hasattr(lib, s), s
+    assert sorted(_lib.SIGNATURES) == syms          # python binding covers the whole header
+    assert _lib.load().pq_b200_abi_version() == _lib.ABI_VERSION
+
+
+def test_argument_errors_without_gpu():
+    lib = _lib.load()
+    parts, n_parts = _lib.parts_array([16])
+    # bad dtype / bad format / bad shape are rejected before any launch
+    assert lib.pq_b200_dequant(1, 16, None, 16, 16, 64, 8, 8, 1, parts, n_parts, 7, None) == -1
+    assert lib.pq_b200_dequant(1, 16, None, 16, 16, 64, 8, 17, 1, parts, n_parts, 0, None) == -2
+    assert lib.pq_b200_dequant(1, 16, None, 16, 16, 63, 8, 8, 1, parts, n_parts, 0, None) == -3
+    assert lib.pq_b200_dequant(1, 16, None, 16, 17, 64, 8, 8, 1, parts, n_parts, 0, None) == -3
+    assert lib.pq_b200_dequant(None, 16, None, 16, 16, 64, 8, 8, 1, parts, n_parts, 0, None) == -6
+    assert lib.pq_b200_dequant(1, 8, None, 16, 16, 64, 8, 8, 1, parts, n_parts, 0, None) == -4
+    assert b"partition" in lib.pq_b200_strerror(-3)
+    with pytest.raises(RuntimeError):
+        _lib.check(-3, "x")
+
+
+def test_no_cpu_path():
+    c = P.PQConfig(8, 8, 1, 1)
+    layer = P.ReplicatedLinear(64, 32, bias=False, params_dtype=torch.float16, quant_config=c)
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        layer(torch.zeros(1, 64, dtype=torch.float16))
+    src = ""
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "vllm_pq_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                src += open(os.path.join(dirpath, f)).read()
+    assert not re.search(r"^\s*(from|import)\s+oracle", src, re.M), "product must not import oracle/"
+
+
+def test_config_mirrors_reference_contract():
+    c = P.PQConfig.from_config({"in_group_size": 8, "nbits_per_codebook": 16, "num_codebooks": 1,
+                                "out_group_size": 1, "quant_method": "aqlm"})
+    assert (c.in_group_size, c.nbits_per_codebook, c.num_codebooks, c.out_group_size) == (8, 16, 1, 1)
+    assert c.pack_factor == 8 and c.get_name() == "pq"
+    assert torch.half in c.get_supported_act_dtypes() and torch.bfloat16 in c.get_supported_act_dtypes()
+    assert P.PQConfig.get_min_capability() == 100 and P.PQConfig.get_config_filenames() == []
+    with pytest.raises(ValueError):
+        P.PQConfig.from_config({"in_group_size": 8})
+    with pytest.raises(AssertionError):
+        P.PQConfig(8, 8, 1, 2)                       # aqlm.py:178-179
+    assert c.get_quant_method(torch.nn.Linear(4, 4), "") is None      # aqlm.py:213-217
+    assert P.get_quantization_config("pq") is P.PQConfig
+    with pytest.raises(ValueError):                  # test_register_quantization_config.py:49-97
+        P.register_quantization_config("pq")(P.PQConfig)
+    with pytest.raises(ValueError):
+        P.register_quantization_config("other")(object)
+
+
+FORMATS = [(8, 8, 1), (8, 8, 2), (16, 8, 1), (4, 4, 1), (12, 16, 1)]
+
+
+@pytest.mark.parametrize("fmt", FORMATS)
+@pytest.mark.parametrize("parts", [[4096, 4096, 4096], [11008, 11008], [4096]])
+def test_create_weights_layout(fmt, parts):
+    b, d, m = fmt
+    method = P.PQLinearMethod(P.PQConfig(d, b, m, 1))
+    layer = torch.nn.Module()
+    with torch.device("meta"):
+        method.create_weights(layer, 4096, parts, 4096, sum(parts), torch.float16, weight_loader=print)
+    n = sum(parts)
+    assert layer.codes.shape == (n, 4096 // d, m) and layer.codes.dtype == P.get_int_dtype(b)
+    assert layer.codebooks.shape == (m * len(parts), 2**b, 1, d) and layer.codebooks.dtype == torch.float16
+    assert layer.scales.shape == (n, 1, 1, 1)
+    assert (layer.codes.input_dim, layer.codes.output_dim, layer.codes.packed_dim, layer.codes.pack_factor) == (1, 0, 1, d)
+    assert layer.codebooks.is_metadata and layer.codebooks.output_partition_sizes == parts
+    assert (layer.scales.output_dim, layer.scales.packed_dim, layer.scales.pack_factor) == (0, 0, 1)
+    assert all(p.weight_loader is print and not p.requires_grad for p in (layer.codes, layer.codebooks, layer.scales))
+
+    if ref_loader.available():                       # same names / shapes / dtypes / attrs as aqlm.py:253-323
+        ref = ref_loader.load_reference_aqlm()
+        rl = torch.nn.Module()
+        with torch.device("meta"):
+            ref.AQLMLinearMethod(ref.AQLMConfig(d, b, m, 1)).create_weights(
+                rl, 4096, parts, 4096, n, torch.float16, weight_loader=print)
+        for name in ("codes", "codebooks", "scales"):
+            a, r = getattr(layer, name), getattr(rl, name)
+            assert a.shape == r.shape and a.dtype == r.dtype, name
+            for attr in ("input_dim", "output_dim", "packed_dim", "pack_factor", "is_metadata",
+                         "output_partition_sizes", "weight_loader"):
+                assert getattr(a, attr, None) == getattr(r, attr, None), (name, attr)
+        assert [n_ for n_, _ in layer.named_parameters()] == [n_ for n_, _ in rl.named_parameters()]
+
+
+def test_create_weights_errors():
+    method = P.PQLinearMethod(P.PQConfig(8, 8, 1, 1))
+    with pytest.raises(ValueError):                  # aqlm.py:238-239 (extended to bf16)
+        method.create_weights(torch.nn.Module(), 64, [8], 64, 8, torch.float32)
+    with pytest.raises(ValueError):                  # aqlm.py:240-244
+        method.create_weights(torch.nn.Module(), 60, [8], 60, 8, torch.float16)
+
+
+def test_fake_ops_trace_shapes():
+    """Meta tensors go through the fake impls (vllm/_custom_ops.py:347-371) - what torch.compile sees."""
+    x = torch.empty(2, 3, 4096, dtype=torch.float16, device="meta")
+    codes = torch.empty(12288, 512, 1, dtype=torch.int16, device="meta")
+    cb = torch.empty(3, 65536, 1, 8, dtype=torch.float16, device="meta")
+    sc = torch.empty(12288, 1, 1, 1, dtype=torch.float16, device="meta")
+    y = torch.ops.pq.gemm(x, codes, cb, sc, [4096] * 3, None)
+    assert y.shape == (2, 3, 12288) and y.dtype == torch.float16
+    w = torch.ops.pq.dequant(codes, cb, [4096] * 3)
+    assert w.shape == (12288, 4096) and w.dtype == torch.float16
+    # schema check of the reference's opcheck (tests/kernels/test_aqlm.py:9-39), minus the CUDA run
+    torch.library.opcheck(torch.ops.pq.dequant.default, (codes, cb, [4096] * 3), test_utils=("test_schema",))
+
+
+def test_tp1_layers_build():
+    cfg = P.PQConfig(8, 8, 2, 1)
+    qkv = P.QKVParallelLinear(4096, 128, 32, 32, bias=False, params_dtype=torch.float16, quant_config=cfg)
+    assert qkv.output_partition_sizes == [4096, 4096, 4096] and qkv.codes.shape == (12288, 512, 2)
+    assert qkv.codebooks.shape == (6, 256, 1, 8)
+    gu = P.MergedColumnParallelLinear(4096, [11008, 11008], bias=False, params_dtype=torch.float16, quant_config=cfg)
+    assert gu.output_partition_sizes == [11008, 11008]
+    down = P.RowParallelLinear(11008, 4096, bias=False, params_dtype=torch.float16, quant_config=cfg)
+    assert down.codes.shape == (4096, 1376, 2) and down.input_size_per_partition == 11008
+    # fused-shard loaders: codebooks land at shard_index * M (linear.py:619-624, 1038-1044)
+    cbk = torch.randn(2, 256, 1, 8).half()
+    qkv.weight_loader(qkv.codebooks, cbk, "k")
+    assert torch.equal(qkv.codebooks.data[2:4], cbk)
+    codes_v = torch.randint(-128, 127, (4096, 512, 2), dtype=torch.int8)
+    qkv.weight_loader(qkv.codes, codes_v, "v")
+    assert torch.equal(qkv.codes.data[8192:], codes_v)
+    up = torch.randn(11008, 1, 1, 1).half()
+    gu.weight_loader(gu.scales, up, 1)
+    assert torch.equal(gu.scales.data[11008:], up)

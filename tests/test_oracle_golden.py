@@ -1,0 +1,85 @@
+"""The oracle against the reference: committed golden vectors (always) and the reference's
+own aqlm.py loaded from /root/reference (only where that tree exists)."""
+import pytest
+import torch
+
+from oracle import pq_oracle as O
+from oracle import ref_loader
+from tests import golden_util as G
+
+
+@pytest.mark.parametrize("name", G.names())
+def test_oracle_matches_golden(name):
+    c = G.load(name)
+    parts = c["partition_sizes"]
+    wu = O.dequantize_partitions(c["codes"], c["codebooks"], parts, None)
+    ws = O.dequantize_partitions(c["codes"], c["codebooks"], parts, c["scales"])
+    assert G.same_bits(wu, c["w_unscaled"])            # P1, bit-exact
+    assert G.same_bits(ws, c["w_scaled"])              # P2, bit-exact
+    y = O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"])
+    assert G.same_bits(y, c["y"])                      # same torch ops on the same weights
+    # the literal embedding_bag formulation (used for the timed CPU baseline) agrees too (fp16)
+    if c["dtype"] == torch.float16:
+        y2 = O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts,
+                                       c["bias"], literal=True)
+        assert G.same_bits(y2, c["y"])
+
+
+def test_golden_covers_corner_codes():
+    c = G.load("c1x8_d8")
+    assert c["codes"].view(-1)[:4].tolist() == [-1, -128, 127, 0]
+    idx = O.unpack_int_data(c["codes"], 8).view(-1)[:4].tolist()
+    assert idx == [255, 128, 127, 0]                   # aqlm.py:32-34
+
+
+def test_unpack_is_mod_2b():
+    import numpy as np
+    a = np.array([-8, -1, 0, 7], dtype=np.int8)
+    assert O.unpack_codes_np(a, 4).tolist() == [8, 15, 0, 7]
+    a = np.array([-32768, -1, 32767], dtype=np.int16)
+    assert O.unpack_codes_np(a, 16).tolist() == [32768, 65535, 32767]
+    a = np.array([-2048, -1, 2047], dtype=np.int16)
+    assert O.unpack_codes_np(a, 12).tolist() == [2048, 4095, 2047]
+
+
+def test_int_dtype_table():
+    assert O.get_int_dtype(4) == torch.int8 and O.get_int_dtype(8) == torch.int8
+    assert O.get_int_dtype(9) == torch.int16 and O.get_int_dtype(16) == torch.int16
+    assert O.get_int_dtype(17) == torch.int32
+    with pytest.raises(ValueError):
+        O.get_int_dtype(65)
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present (GPU box)")
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2), (16, 8, 1), (4, 4, 1), (12, 16, 1), (8, 8, 4),
+                                 (8, 8, 8), (4, 8, 2), (8, 16, 1), (12, 4, 1)])
+def test_oracle_matches_live_reference(fmt):
+    ref = ref_loader.load_reference_aqlm()
+    b, d, m = fmt
+    parts = [40, 24, 24]
+    c = O.make_case(parts, 16 * d, b, d, m, t=3, dtype=torch.float16, seed=7, bias=True,
+                    positive_scales=False)
+    off = 0
+    for p, n_p in enumerate(parts):
+        cu = ref.unpack_int_data(c["codes"][off:off + n_p], b)
+        for s in (None, c["scales"][off:off + n_p]):
+            wr = ref.dequantize_weight(cu, c["codebooks"][p * m:(p + 1) * m], s)
+            wo = O.dequantize_weight(cu, c["codebooks"][p * m:(p + 1) * m], s)
+            assert G.same_bits(wr, wo)
+        off += n_p
+    yr = ref.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"])
+    yo = O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"])
+    assert G.same_bits(yr, yo)
+    assert ref.get_int_dtype(b) == O.get_int_dtype(b)
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present (GPU box)")
+def test_reference_bf16_single_codebook_matches():
+    """bf16 is an extension (reference: fp16 only, aqlm.py:238-239). For M=1 the reference's torch
+    functions still run and agree with the oracle; for M>=2 CPU embedding_bag does not round to
+    nearest even in bf16, so the oracle's fp32-sum + RNE is the definition."""
+    ref = ref_loader.load_reference_aqlm()
+    c = O.make_case([64], 128, 8, 8, 1, t=2, dtype=torch.bfloat16, seed=3)
+    cu = ref.unpack_int_data(c["codes"], 8)
+    assert G.same_bits(ref.dequantize_weight(cu, c["codebooks"], c["scales"]),
+                       O.dequantize_weight(cu, c["codebooks"], c["scales"]))

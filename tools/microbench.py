@@ -1,0 +1,109 @@
+"""Per-kernel timing on one GPU: rotates through enough distinct weight sets that codes do not
+stay L2-resident (>= 256 MB per timed loop), CUDA events on the launching stream."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import vllm_pq_b200 as P  # noqa: E402
+from vllm_pq_b200 import _lib  # noqa: E402
+
+HBM_GBS = 6524.6
+SHAPES = {
+    "sq4096": ([4096], 4096),
+    "qkv7b": ([4096] * 3, 4096),
+    "o7b": ([4096], 4096),
+    "gateup7b": ([11008] * 2, 4096),
+    "down7b": ([4096], 11008),
+    "gateup70b": ([28672] * 2, 8192),
+    "down70b": ([8192], 28672),
+}
+
+
+def algo_bytes(t, n, k, d, b, m, p):
+    sc = 1 if b <= 8 else 2
+    return n * (k // d) * m * sc + p * m * (1 << b) * d * 2 + n * 2 + t * k * 2 + t * n * 2
+
+
+def make(parts, k, b, d, m, dtype, nrep):
+    n = sum(parts)
+    e = 1 << b
+    sets = []
+    for _ in range(nrep):
+        codes = torch.randint(-(e // 2), e // 2, (n, k // d, m), device="cuda", dtype=torch.int32).to(
+            torch.int8 if b <= 8 else torch.int16)
+        cb = torch.randn(len(parts) * m, e, 1, d, device="cuda", dtype=dtype)
+        sc = (torch.rand(n, 1, 1, 1, device="cuda") + 0.5).to(dtype)
+        sets.append((codes, cb, sc))
+    return sets
+
+
+def time_loop(fn, sets, iters):
+    for s in sets[:2]:
+        fn(s)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        for s in sets:
+            fn(s)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / (iters * len(sets))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shapes", default="sq4096,qkv7b,gateup7b,down7b")
+    ap.add_argument("--formats", default="8x8x1,8x8x2,16x8x1")
+    ap.add_argument("--tokens", default="1,4")
+    ap.add_argument("--algos", default="auto")
+    ap.add_argument("--dtype", default="fp16")
+    ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--dequant", type=int, default=1)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    dtype = torch.float16 if a.dtype == "fp16" else torch.bfloat16
+    P.ops.set_pdl(bool(a.pdl))
+    names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3}
+    rows = []
+    for sname in a.shapes.split(","):
+        parts, k = SHAPES[sname]
+        n = sum(parts)
+        for f in a.formats.split(","):
+            b, d, m = (int(v) for v in f.split("x"))
+            code_bytes = n * (k // d) * m * (1 if b <= 8 else 2)
+            nrep = max(2, min(64, (256 << 20) // code_bytes + 1))
+            sets = make(parts, k, b, d, m, dtype, nrep)
+            if a.dequant:
+                out_bytes = n * k * 2
+                dt = time_loop(lambda s: P.ops.pq_dequant(s[0], s[1], parts), sets[:max(2, (512 << 20) // out_bytes)], 3)
+                rows.append(dict(shape=sname, fmt=f, op="dequant", us=dt * 1e6,
+                                 gbs=(out_bytes + code_bytes) / dt / 1e9))
+                print(rows[-1], flush=True)
+            for t in (int(v) for v in a.tokens.split(",")):
+                x = torch.randn(t, k, device="cuda", dtype=dtype)
+                for an in a.algos.split(","):
+                    algo = names[an]
+                    try:
+                        dt = time_loop(lambda s: P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=algo), sets, 5)
+                    except RuntimeError as exc:
+                        print(f"skip {sname} {f} t={t} {an}: {exc}")
+                        continue
+                    ab = algo_bytes(t, n, k, d, b, m, len(parts))
+                    rows.append(dict(shape=sname, fmt=f, op="gemm", algo=an, t=t, us=dt * 1e6,
+                                     gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
+                                     tflops=2 * t * n * k / dt / 1e12))
+                    print(rows[-1], flush=True)
+            del sets
+            torch.cuda.empty_cache()
+    if a.out:
+        with open(a.out, "w") as fh:
+            json.dump(rows, fh, indent=1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,193 @@
+"""torch custom ops ``pq::gemm`` / ``pq::dequant`` over the C ABI.
+
+Mirror of the reference's op boundary for this path:
+  torch.ops._C.aqlm_gemm / aqlm_dequant   csrc/torch_bindings.cpp:161-173
+  python wrappers                          vllm/_custom_ops.py:646-658
+  fake (meta) implementations              vllm/_custom_ops.py:347-371
+Same argument order and meaning, same output shape rules, RuntimeError for an
+unsupported request (TORCH_CHECK in gemm_kernels.cu:539-540).  Differences:
+``dequant`` derives in_features from the codebook's subvector length instead of
+hard-coding 8 (gemm_kernels.cu:557), and both accept bf16.
+
+The CUDA implementation only reads its inputs and returns a fresh tensor
+(SURVEY.md 8b "Ownership"); it launches on torch's current stream, does not
+synchronise and does not allocate outside torch's allocator, so it can be
+captured in a CUDA graph (model_runner.py:1428-1562 in the reference).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from . import _lib
+
+_DTYPES = {torch.float16: _lib.PQ_F16, torch.bfloat16: _lib.PQ_BF16}
+
+_LIBRARY = torch.library.Library("pq", "DEF")
+_LIBRARY.define("gemm(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
+                "int[] codebook_partition_sizes, Tensor? bias) -> Tensor")
+_LIBRARY.define("gemm_algo(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
+                "int[] codebook_partition_sizes, Tensor? bias, int algo) -> Tensor")
+_LIBRARY.define("dequant(Tensor codes, Tensor codebooks, int[] codebook_partition_sizes) -> Tensor")
+_LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
+                "int[] codebook_partition_sizes) -> Tensor")
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _format(codes: torch.Tensor, codebooks: torch.Tensor, parts: List[int]):
+    if codes.dim() != 3 or codebooks.dim() != 4:
+        raise RuntimeError("PQ: codes must be [N, G, M] and codebooks [P*M, E, 1, d]")
+    if codebooks.dtype not in _DTYPES:
+        raise RuntimeError(f"PQ: codebooks dtype {codebooks.dtype} not supported (fp16/bf16)")
+    parts = list(parts) if len(parts) else [codes.shape[0]]
+    n, g, m = codes.shape
+    pm, e, og, d = codebooks.shape
+    if og != 1:
+        raise RuntimeError("PQ: out_group_size must be 1")          # aqlm.py:178-179
+    if pm != m * len(parts) or (e & (e - 1)) != 0:
+        raise RuntimeError(f"PQ with {pm / len(parts)} codebooks and {e} entries is not "
+                           "currently supported.")                 # gemm_kernels.cu:539
+    nbits = e.bit_length() - 1
+    want = torch.int8 if nbits <= 8 else torch.int16
+    if codes.dtype != want:
+        raise RuntimeError(f"PQ: {nbits}-bit codes must be stored as {want}, got {codes.dtype}")
+    if not codes.is_contiguous() or not codebooks.is_contiguous():
+        raise RuntimeError("PQ: codes and codebooks must be contiguous")
+    return parts, n, g, m, d, nbits
+
+
+def _require_cuda(t: torch.Tensor):
+    if not t.is_cuda:
+        raise RuntimeError("PQ kernels are CUDA (sm_100a) only; there is no CPU path")
+
+
+def _dequant_impl(codes, codebooks, scales, parts):
+    _require_cuda(codes)
+    lib = _lib.load()
+    parts, n, g, m, d, nbits = _format(codes, codebooks, parts)
+    if scales is not None:
+        if scales.dtype != codebooks.dtype or scales.numel() != n or not scales.is_contiguous():
+            raise RuntimeError("PQ: scales must be contiguous [N,1,1,1] of the codebook dtype")
+    out = torch.empty((n, g * d), dtype=codebooks.dtype, device=codebooks.device)
+    arr, np_ = _lib.parts_array(parts)
+    with torch.cuda.device(codes.device):
+        rc = lib.pq_b200_dequant(codes.data_ptr(), codebooks.data_ptr(), _ptr(scales), out.data_ptr(),
+                                 n, g * d, d, nbits, m, arr, np_, _DTYPES[codebooks.dtype],
+                                 torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "pq::dequant")
+    return out
+
+
+def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo):
+    _require_cuda(input)
+    lib = _lib.load()
+    parts, n, g, m, d, nbits = _format(codes, codebooks, parts)
+    k = g * d
+    if input.shape[-1] != k:
+        raise RuntimeError(f"PQ: input has {input.shape[-1]} features, weight has {k}")
+    dt = input.dtype
+    if dt not in _DTYPES or codebooks.dtype != dt or scales.dtype != dt:
+        raise RuntimeError("PQ: input, codebooks and scales must share one of fp16/bf16")
+    if scales.numel() != n or not scales.is_contiguous():
+        raise RuntimeError("PQ: scales must be contiguous [N,1,1,1]")
+    if bias is not None and (bias.dtype != dt or bias.numel() != n or not bias.is_contiguous()):
+        raise RuntimeError("PQ: bias must be contiguous [N] of the input dtype")
+    x = input.reshape(-1, k)
+    if x.stride(-1) != 1 or (x.stride(0) * 2) % 16 or x.data_ptr() % 16:
+        x = x.contiguous()
+    t = x.shape[0]
+    out = torch.empty((t, n), dtype=dt, device=input.device)
+    if t == 0:
+        return out.reshape(input.shape[:-1] + (n,))
+    arr, np_ = _lib.parts_array(parts)
+    with torch.cuda.device(input.device):
+        if algo == _lib.ALGO_AUTO:
+            algo = lib.pq_b200_pick_algo(t, n, k, d, nbits, m)
+        ws_bytes = lib.pq_b200_workspace_bytes(algo, t, n, k, d, nbits, m, np_)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=input.device) if ws_bytes else None
+        rc = lib.pq_b200_gemm(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
+                              scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
+                              arr, np_, _DTYPES[dt], algo, _ptr(ws), ws_bytes,
+                              torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "pq::gemm")
+    return out.reshape(input.shape[:-1] + (n,))
+
+
+def _gemm_cuda(input, codes, codebooks, scales, codebook_partition_sizes, bias):
+    return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, _lib.ALGO_AUTO)
+
+
+def _gemm_algo_cuda(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo):
+    return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo)
+
+
+def _dequant_cuda(codes, codebooks, codebook_partition_sizes):
+    return _dequant_impl(codes, codebooks, None, codebook_partition_sizes)
+
+
+def _dequant_scaled_cuda(codes, codebooks, scales, codebook_partition_sizes):
+    return _dequant_impl(codes, codebooks, scales, codebook_partition_sizes)
+
+
+_LIBRARY.impl("gemm", _gemm_cuda, "CUDA")
+_LIBRARY.impl("gemm_algo", _gemm_algo_cuda, "CUDA")
+_LIBRARY.impl("dequant", _dequant_cuda, "CUDA")
+_LIBRARY.impl("dequant_scaled", _dequant_scaled_cuda, "CUDA")
+
+
+# ---- fake (meta) implementations: shape rules of vllm/_custom_ops.py:347-371 -------
+def _gemm_fake(input, codes, codebooks, scales, codebook_partition_sizes, bias):
+    out_features = codes.size(0) * codebooks.size(2)
+    flat_input = input.reshape((-1, input.size(-1)))
+    flat_output = torch.empty((flat_input.size(0), out_features), dtype=input.dtype,
+                              device=input.device)
+    output_sizes = list(input.shape)
+    output_sizes.pop()
+    output_sizes.append(-1)
+    return flat_output.reshape(tuple(output_sizes))
+
+
+def _gemm_algo_fake(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo):
+    return _gemm_fake(input, codes, codebooks, scales, codebook_partition_sizes, bias)
+
+
+def _dequant_fake(codes, codebooks, codebook_partition_sizes):
+    in_features = codes.size(1) * codebooks.size(3)
+    out_features = codes.size(0)
+    return torch.empty((out_features, in_features), dtype=codebooks.dtype, device=codebooks.device)
+
+
+def _dequant_scaled_fake(codes, codebooks, scales, codebook_partition_sizes):
+    return _dequant_fake(codes, codebooks, codebook_partition_sizes)
+
+
+torch.library.register_fake("pq::gemm")(_gemm_fake)
+torch.library.register_fake("pq::gemm_algo")(_gemm_algo_fake)
+torch.library.register_fake("pq::dequant")(_dequant_fake)
+torch.library.register_fake("pq::dequant_scaled")(_dequant_scaled_fake)
+
+
+# ---- python wrappers, named after vllm/_custom_ops.py:646-658 ------------------------
+def pq_gemm(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor,
+            scales: torch.Tensor, codebook_partition_sizes: List[int],
+            bias: Optional[torch.Tensor], algo: int = _lib.ALGO_AUTO) -> torch.Tensor:
+    if algo == _lib.ALGO_AUTO:
+        return torch.ops.pq.gemm(input, codes, codebooks, scales, codebook_partition_sizes, bias)
+    return torch.ops.pq.gemm_algo(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo)
+
+
+def pq_dequant(codes: torch.Tensor, codebooks: torch.Tensor,
+               codebook_partition_sizes: List[int],
+               scales: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if scales is None:
+        return torch.ops.pq.dequant(codes, codebooks, codebook_partition_sizes)
+    return torch.ops.pq.dequant_scaled(codes, codebooks, scales, codebook_partition_sizes)
+
+
+def set_pdl(enabled: bool) -> None:
+    """Programmatic dependent launch for the decode kernels (see csrc/pq_common.cuh)."""
+    _lib.load().pq_b200_set_pdl(1 if enabled else 0)

@@ -1,0 +1,166 @@
+// One-shot all-reduce over NVLink peer memory: the tensor-parallel reduction hook
+// after the row-parallel PQ linears (o_proj, down_proj).
+//
+// Replaces cross_device_reduce_1stage + multi_gpu_barrier + the eager-mode staging
+// memcpy of the reference (csrc/custom_all_reduce.cuh:178-230, custom_all_reduce.cu:75-77):
+//   push   every rank writes its vector straight into slot [rank] of every peer's staging
+//          buffer with 128-bit stores (no separate memcpy, no registration of the input)
+//   signal per-block flag, st.release.sys, value = epoch
+//   wait   ld.acquire.sys on this rank's flags until all peers show the epoch
+//   sum    local read of world slots, fp32 accumulate in rank order 0..world-1 on every
+//          rank -> bitwise identical results (custom_all_reduce.cuh:204-212)
+// The epoch lives in device memory and is advanced by the kernel itself, so a launch
+// carries no host-side state and can be replayed from a CUDA graph. Two staging slots
+// alternate by epoch parity: a rank can only run one epoch ahead of its slowest peer
+// (it needs that peer's flag to finish), so the slot it overwrites is never being read.
+//
+// Decode messages are 8-16 KiB: latency-bound, one CTA per 8 KiB.
+#include <string.h>
+
+#include "pq_common.cuh"
+
+namespace pq {
+
+constexpr int kArThreads = 512;
+constexpr int kArMaxBlocks = 36;
+// flag buffer layout (uint32 words): [block * world + peer] ... then
+constexpr int kArCounterWord = 1000;   // this rank's epoch counter
+constexpr int kArTicketWord = 1001;    // block-completion ticket
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+struct ArPeers {
+  unsigned char* data[PQ_AR_MAX_WORLD];
+  uint32_t* flags[PQ_AR_MAX_WORLD];
+};
+
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(kArThreads)
+pq_allreduce_oneshot_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int n_vec,
+                            ArPeers peers, int rank, long long slot_bytes) {
+  uint32_t* my_flags = peers.flags[rank];
+  const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(my_flags + kArCounterWord) + 1u;
+  const long long slot_off = (long long)(epoch & 1u) * WORLD * slot_bytes;
+  const int per_block = (n_vec + gridDim.x - 1) / gridDim.x;
+  const int v0 = blockIdx.x * per_block;
+  const int v1 = min(v0 + per_block, n_vec);
+
+  // push this block's range into every peer (self included: a local copy)
+  for (int v = v0 + threadIdx.x; v < v1; v += kArThreads) {
+    const uint4 val = in[v];
+#pragma unroll
+    for (int p = 0; p < WORLD; ++p) {
+      const int peer = (rank + p) % WORLD;               // spread the links
+      reinterpret_cast<uint4*>(peers.data[peer] + slot_off + (long long)rank * slot_bytes)[v] = val;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < WORLD) {
+    __threadfence_system();
+    st_release_sys(peers.flags[threadIdx.x] + blockIdx.x * WORLD + rank, epoch);
+    while (ld_acquire_sys(my_flags + blockIdx.x * WORLD + threadIdx.x) != epoch) {}
+  }
+  __syncthreads();
+
+  const unsigned char* mine = peers.data[rank] + slot_off;
+  for (int v = v0 + threadIdx.x; v < v1; v += kArThreads) {
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) {
+      const uint4 val = ld_cg_16(reinterpret_cast<const uint4*>(mine + (long long)q * slot_bytes) + v);
+      const uint32_t w[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = Traits<T>::to_f2(w[i]);
+        acc[2 * i] += f.x;
+        acc[2 * i + 1] += f.y;
+      }
+    }
+    out[v] = make_uint4(Traits<T>::pack(acc[0], acc[1]), Traits<T>::pack(acc[2], acc[3]),
+                        Traits<T>::pack(acc[4], acc[5]), Traits<T>::pack(acc[6], acc[7]));
+  }
+
+  // last block to finish advances the epoch (every block read it before arriving here)
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(my_flags + kArTicketWord, 1u);
+    if (done == gridDim.x - 1) {
+      my_flags[kArTicketWord] = 0u;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(my_flags + kArCounterWord) = epoch;
+    }
+  }
+}
+
+template <typename T>
+static int launch_ar(const void* in, void* out, int n_vec, const ArPeers& peers, int rank, int world,
+                     long long slot_bytes, cudaStream_t stream) {
+  int blocks = (n_vec + kArThreads - 1) / kArThreads;
+  if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
+  if (blocks < 1) blocks = 1;
+#define PQ_AR(W)                                                                              \
+  pq_allreduce_oneshot_kernel<T, W><<<blocks, kArThreads, 0, stream>>>(                       \
+      (const uint4*)in, (uint4*)out, n_vec, peers, rank, slot_bytes)
+  switch (world) {
+    case 2: PQ_AR(2); break;
+    case 4: PQ_AR(4); break;
+    case 8: PQ_AR(8); break;
+    default: return PQ_ERR_UNSUPPORTED;
+  }
+#undef PQ_AR
+  return (int)cudaGetLastError();
+}
+
+int allreduce_oneshot_dispatch(const void* in, void* out, int64_t n_elems, int dtype,
+                               void* const* peer_data, void* const* peer_flags, int rank, int world,
+                               int64_t slot_bytes_in, cudaStream_t stream) {
+  ArPeers peers{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_data[r] || !peer_flags[r]) return PQ_ERR_NULL;
+    peers.data[r] = (unsigned char*)peer_data[r];
+    peers.flags[r] = (uint32_t*)peer_flags[r];
+  }
+  const int n_vec = (int)(n_elems * 2 / 16);
+  const long long slot_bytes = (long long)slot_bytes_in;
+  return dtype == PQ_F16 ? launch_ar<__half>(in, out, n_vec, peers, rank, world, slot_bytes, stream)
+                         : launch_ar<__nv_bfloat16>(in, out, n_vec, peers, rank, world, slot_bytes, stream);
+}
+
+}  // namespace pq
+
+// ---- buffer + IPC helpers (host) ----------------------------------------------------------
+extern "C" {
+
+PQ_API int pq_b200_malloc(int64_t bytes, void** out) {
+  if (!out || bytes <= 0) return PQ_ERR_NULL;
+  return (int)cudaMalloc(out, (size_t)bytes);
+}
+PQ_API int pq_b200_free(void* p) { return (int)cudaFree(p); }
+PQ_API int pq_b200_memset_async(void* p, int value, int64_t bytes, void* stream) {
+  return (int)cudaMemsetAsync(p, value, (size_t)bytes, (cudaStream_t)stream);
+}
+PQ_API int pq_b200_ipc_get_handle(void* ptr, void* handle64) {
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, ptr);
+  if (e != cudaSuccess) return (int)e;
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+PQ_API int pq_b200_ipc_open_handle(void* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  return (int)cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess);
+}
+PQ_API int pq_b200_ipc_close_handle(void* p) { return (int)cudaIpcCloseMemHandle(p); }
+
+}  // extern "C"

@@ -1,0 +1,131 @@
+// extern "C" surface of libpq_b200.so (see include/pq_b200.h).
+// Validates arguments, picks the kernel family, launches on the caller's stream.
+#include "pq_common.cuh"
+
+namespace pq {
+int dequant_dispatch(const void*, const void*, const void*, void*, int64_t, int64_t, int, int, int,
+                     const int64_t*, int, int, cudaStream_t);
+int gemv_direct_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
+                         void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
+                         int, int, cudaStream_t);
+int gemv_lut_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
+                      void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
+                      int, int, void*, int64_t, cudaStream_t);
+int64_t gemv_lut_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
+bool gemv_lut_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
+                     void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
+                     int, int, void*, int64_t, cudaStream_t);
+int64_t gemm_tc_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
+bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+int allreduce_oneshot_dispatch(const void*, void*, int64_t, int, void* const*, void* const*, int, int,
+                               int64_t, cudaStream_t);
+extern bool g_use_pdl;
+}  // namespace pq
+
+static int check_format(int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                        int n_parts, int dtype) {
+  if (dtype != PQ_F16 && dtype != PQ_BF16) return PQ_ERR_DTYPE;
+  if (nbits < 1 || nbits > 16 || d < 1 || d > 64 || m < 1 || m > 16) return PQ_ERR_FORMAT;
+  if (n <= 0 || k <= 0 || k % d != 0 || n > INT32_MAX || k > INT32_MAX) return PQ_ERR_SHAPE;
+  if (part_sizes == nullptr) return PQ_ERR_NULL;
+  if (n_parts < 1 || n_parts > PQ_MAX_PARTS) return PQ_ERR_SHAPE;
+  int64_t s = 0;
+  for (int i = 0; i < n_parts; ++i) {
+    if (part_sizes[i] <= 0) return PQ_ERR_SHAPE;
+    s += part_sizes[i];
+  }
+  return s == n ? PQ_OK : PQ_ERR_SHAPE;
+}
+
+extern "C" {
+
+int pq_b200_abi_version(void) { return PQ_B200_ABI_VERSION; }
+
+const char* pq_b200_strerror(int code) {
+  switch (code) {
+    case PQ_OK: return "ok";
+    case PQ_ERR_DTYPE: return "dtype must be PQ_F16 or PQ_BF16";
+    case PQ_ERR_FORMAT: return "PQ format (nbits, d, m) not supported";
+    case PQ_ERR_SHAPE: return "bad shape: k % d != 0, non-positive size, or partition sizes do not sum to n";
+    case PQ_ERR_ALIGN: return "pointer or stride not aligned to 16 bytes";
+    case PQ_ERR_WORKSPACE: return "workspace too small";
+    case PQ_ERR_NULL: return "required pointer is NULL";
+    case PQ_ERR_UNSUPPORTED: return "no kernel for this request";
+    case PQ_ERR_DEVICE: return "device is not sm_100";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+  }
+}
+
+void pq_b200_set_pdl(int enabled) { pq::g_use_pdl = enabled != 0; }
+
+int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales, void* w_out,
+                    int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                    int n_parts, int dtype, void* stream) {
+  int rc = check_format(n, k, d, nbits, m, part_sizes, n_parts, dtype);
+  if (rc) return rc;
+  if (!codes || !codebooks || !w_out) return PQ_ERR_NULL;
+  if (((uintptr_t)codebooks | (uintptr_t)w_out) & 15) return PQ_ERR_ALIGN;
+  return pq::dequant_dispatch(codes, codebooks, scales, w_out, n, k, d, nbits, m, part_sizes, n_parts,
+                              dtype, (cudaStream_t)stream);
+}
+
+int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  if (t > 8 && pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMM_TC;
+  if (pq::gemv_lut_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
+  return PQ_ALGO_GEMV_DIRECT;
+}
+
+int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                                int n_parts) {
+  if (algo == PQ_ALGO_AUTO) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
+  if (algo == PQ_ALGO_GEMV_LUT) return pq::gemv_lut_workspace(t, n, k, d, nbits, m, n_parts);
+  if (algo == PQ_ALGO_GEMM_TC) return pq::gemm_tc_workspace(t, n, k, d, nbits, m, n_parts);
+  return 0;
+}
+
+int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                 const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                 int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                 int n_parts, int dtype, int algo, void* workspace, int64_t workspace_bytes,
+                 void* stream) {
+  int rc = check_format(n, k, d, nbits, m, part_sizes, n_parts, dtype);
+  if (rc) return rc;
+  if (!x || !codes || !codebooks || !scales || !y) return PQ_ERR_NULL;
+  if (t <= 0 || t > INT32_MAX || x_stride < k || y_stride < n) return PQ_ERR_SHAPE;
+  if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
+  if (algo == PQ_ALGO_AUTO) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (algo) {
+    case PQ_ALGO_GEMV_DIRECT:
+      return pq::gemv_direct_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k,
+                                      d, nbits, m, part_sizes, n_parts, dtype, s);
+    case PQ_ALGO_GEMV_LUT:
+      if (!pq::gemv_lut_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+      if (workspace_bytes < pq::gemv_lut_workspace(t, n, k, d, nbits, m, n_parts) || !workspace)
+        return PQ_ERR_WORKSPACE;
+      return pq::gemv_lut_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
+                                   nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+    case PQ_ALGO_GEMM_TC:
+      if (!pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+      if (workspace_bytes < pq::gemm_tc_workspace(t, n, k, d, nbits, m, n_parts)) return PQ_ERR_WORKSPACE;
+      return pq::gemm_tc_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
+                                  nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+    default:
+      return PQ_ERR_UNSUPPORTED;
+  }
+}
+
+int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems, int dtype,
+                              void* const* peer_data, void* const* peer_flags, int rank, int world,
+                              int64_t slot_bytes, void* stream) {
+  if (dtype != PQ_F16 && dtype != PQ_BF16) return PQ_ERR_DTYPE;
+  if (!in || !out || !peer_data || !peer_flags) return PQ_ERR_NULL;
+  if (world < 2 || world > PQ_AR_MAX_WORLD || rank < 0 || rank >= world || n_elems <= 0) return PQ_ERR_SHAPE;
+  if ((n_elems * 2) % 16 || slot_bytes % 16 || ((uintptr_t)in | (uintptr_t)out) & 15) return PQ_ERR_ALIGN;
+  if (n_elems * 2 > slot_bytes) return PQ_ERR_WORKSPACE;
+  return pq::allreduce_oneshot_dispatch(in, out, n_elems, dtype, peer_data, peer_flags, rank, world, slot_bytes,
+                                        (cudaStream_t)stream);
+}
+
+}  // extern "C"

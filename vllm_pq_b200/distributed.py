@@ -1,0 +1,170 @@
+"""Tensor-parallel state and the reduction hook of the row-parallel PQ linears.
+
+One process per GPU; ``torch.distributed`` (NCCL on GPUs, gloo in CPU tests)
+is the plumbing.  Mirrors the one call chain of the reference that the PQ path
+reaches:
+  tensor_model_parallel_all_reduce   vllm/distributed/communication_op.py:11-13
+  GroupCoordinator.all_reduce        vllm/distributed/parallel_state.py:287-313
+  CudaCommunicator.all_reduce        device_communicators/cuda_communicator.py:52-72
+  CustomAllreduce                    device_communicators/custom_all_reduce.py:55-298
+Decode-sized messages go through the one-shot NVLink kernel in
+csrc/pq_allreduce.cu (each rank pushes its vector into every peer's buffer, one
+flag barrier, local fp32 sum in rank order); larger ones through NCCL.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+_TP_GROUP: Optional[dist.ProcessGroup] = None
+_TP_RANK = 0
+_TP_WORLD = 1
+_ONESHOT: Optional["OneShotAllReduce"] = None
+
+
+def init_tensor_parallel(group: Optional[dist.ProcessGroup] = None, oneshot: Optional[bool] = None,
+                         max_oneshot_bytes: int = 1 << 20) -> None:
+    """All ranks of ``group`` (default: the world) form one TP group
+    (parallel_state.py:865-923 with pp = dp = 1)."""
+    global _TP_GROUP, _TP_RANK, _TP_WORLD, _ONESHOT
+    if not dist.is_initialized():
+        _TP_GROUP, _TP_RANK, _TP_WORLD, _ONESHOT = None, 0, 1, None
+        return
+    _TP_GROUP = group if group is not None else dist.group.WORLD
+    _TP_RANK = dist.get_rank(_TP_GROUP)
+    _TP_WORLD = dist.get_world_size(_TP_GROUP)
+    _ONESHOT = None
+    if oneshot is None:
+        oneshot = os.environ.get("PQ_ONESHOT_ALLREDUCE", "1") != "0"
+    if (oneshot and _TP_WORLD in (2, 4, 8) and torch.cuda.is_available()
+            and dist.get_backend(_TP_GROUP) == "nccl"):
+        try:
+            _ONESHOT = OneShotAllReduce(_TP_GROUP, max_oneshot_bytes)
+        except Exception as exc:  # peer access unavailable: NCCL only, said out loud
+            if _TP_RANK == 0:
+                print(f"[vllm_pq_b200] one-shot all-reduce disabled: {exc}")
+            _ONESHOT = None
+
+
+def destroy_tensor_parallel() -> None:
+    global _TP_GROUP, _TP_RANK, _TP_WORLD, _ONESHOT
+    if _ONESHOT is not None:
+        _ONESHOT.close()
+    _TP_GROUP, _TP_RANK, _TP_WORLD, _ONESHOT = None, 0, 1, None
+
+
+def get_tensor_model_parallel_world_size() -> int:
+    return _TP_WORLD
+
+
+def get_tensor_model_parallel_rank() -> int:
+    return _TP_RANK
+
+
+def oneshot_enabled() -> bool:
+    return _ONESHOT is not None
+
+
+def tensor_model_parallel_all_reduce(input_: torch.Tensor) -> torch.Tensor:
+    """All-reduce SUM across the TP group; passthrough at world size 1
+    (parallel_state.py:303-304)."""
+    if _TP_WORLD == 1:
+        return input_
+    if _ONESHOT is not None and _ONESHOT.eligible(input_):
+        return _ONESHOT.all_reduce(input_)
+    dist.all_reduce(input_, group=_TP_GROUP)     # input_ is a fresh GEMM output: in place is safe
+    return input_
+
+
+def tensor_model_parallel_all_gather(input_: torch.Tensor, dim: int = -1) -> torch.Tensor:
+    """Only reached with gather_output=True, which the Llama layers never set
+    (linear.py:426-428,787)."""
+    if _TP_WORLD == 1:
+        return input_
+    dim = dim % input_.dim()
+    parts = [torch.empty_like(input_) for _ in range(_TP_WORLD)]
+    dist.all_gather(parts, input_.contiguous(), group=_TP_GROUP)
+    return torch.cat(parts, dim=dim)
+
+
+class OneShotAllReduce:
+    """Host side of pq_b200_allreduce_oneshot: owns this rank's staging + flag
+    buffers (cudaMalloc'd by the C library so the IPC handle maps the exact base),
+    exchanges cudaIpc handles over the process group, keeps the epoch counter.
+    Eligibility follows custom_all_reduce.py:247-260: fp16/bf16, 16-byte multiple,
+    at most ``max_bytes``; world size 2/4/8 on one NVSwitch node."""
+
+    def __init__(self, group: dist.ProcessGroup, max_bytes: int):
+        from . import _lib
+        self._libmod = _lib
+        self.lib = _lib.load()
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.max_bytes = int(max_bytes)
+        self._opened: List[int] = []
+        # two staging slots (alternating by the device-side epoch parity) so that a fast
+        # rank's next push cannot overwrite data a slow rank is still summing
+        self.data = self._malloc(2 * self.world * self.max_bytes)
+        self.flags = self._malloc(_lib.AR_FLAG_BYTES)
+        stream = torch.cuda.current_stream().cuda_stream
+        _lib.check(self.lib.pq_b200_memset_async(self.flags, 0, _lib.AR_FLAG_BYTES, stream), "memset")
+        torch.cuda.synchronize()
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (self._handle(self.data), self._handle(self.flags)), group=group)
+        self.peer_data = (ctypes.c_void_p * self.world)()
+        self.peer_flags = (ctypes.c_void_p * self.world)()
+        for r, (hd, hf) in enumerate(handles):
+            if r == self.rank:
+                self.peer_data[r], self.peer_flags[r] = self.data, self.flags
+            else:
+                self.peer_data[r] = self._open(hd)
+                self.peer_flags[r] = self._open(hf)
+        dist.barrier(group=group)
+
+    def _malloc(self, nbytes: int) -> int:
+        p = ctypes.c_void_p()
+        self._libmod.check(self.lib.pq_b200_malloc(nbytes, ctypes.byref(p)), "pq_b200_malloc")
+        return p.value
+
+    def _handle(self, ptr: int) -> bytes:
+        buf = ctypes.create_string_buffer(64)
+        self._libmod.check(self.lib.pq_b200_ipc_get_handle(ptr, buf), "ipc_get_handle")
+        return buf.raw
+
+    def _open(self, handle: bytes) -> int:
+        p = ctypes.c_void_p()
+        buf = ctypes.create_string_buffer(handle, 64)
+        self._libmod.check(self.lib.pq_b200_ipc_open_handle(buf, ctypes.byref(p)), "ipc_open_handle")
+        self._opened.append(p.value)
+        return p.value
+
+    def eligible(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return (t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous()
+                and nbytes % 16 == 0 and nbytes <= self.max_bytes and t.data_ptr() % 16 == 0)
+
+    def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
+        out = torch.empty_like(t)
+        dt = self._libmod.PQ_F16 if t.dtype == torch.float16 else self._libmod.PQ_BF16
+        rc = self.lib.pq_b200_allreduce_oneshot(t.data_ptr(), out.data_ptr(), t.numel(), dt,
+                                                self.peer_data, self.peer_flags, self.rank, self.world,
+                                                self.max_bytes,
+                                                torch.cuda.current_stream().cuda_stream)
+        self._libmod.check(rc, "pq_b200_allreduce_oneshot")
+        return out
+
+    def close(self) -> None:
+        try:
+            torch.cuda.synchronize()
+            for p in self._opened:
+                self.lib.pq_b200_ipc_close_handle(p)
+            self.lib.pq_b200_free(self.data)
+            self.lib.pq_b200_free(self.flags)
+        except Exception:
+            pass
+        self._opened = []

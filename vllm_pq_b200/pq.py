@@ -1,0 +1,163 @@
+"""PQConfig / PQLinearMethod: the product-quantization linear method.
+
+Drop-in for the reference's AQLMConfig / AQLMLinearMethod
+(vllm/model_executor/layers/quantization/aqlm.py:159-374): same constructor
+arguments, same HF ``quantization_config`` keys, same parameter names, shapes,
+dtypes and loader attributes in ``create_weights`` (aqlm.py:253-323), same
+``apply(layer, x, bias)`` contract - so the reference's unmodified weight
+loaders (linear.py:370-408, 494-640, 873-1058, 1144-1180) fill the parameters.
+
+What changes is below the op boundary: every (nbits, d, M) format runs on the
+sm_100a kernels in csrc/ (the reference has CUDA kernels for 1x16 and 2x8 only
+and sends everything else through torch ops, aqlm.py:344-374), fp16 *and* bf16
+are accepted (reference: fp16 only, aqlm.py:193-194,238-239), and there is no
+CPU path.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional
+
+import torch
+from torch.nn.parameter import Parameter
+
+from . import _custom_ops as ops
+from .plugin_api import (LinearMethodBase, QuantizationConfig, register_quantization_config,
+                         set_weight_attrs)
+
+
+def get_int_dtype(nbits: int) -> torch.dtype:
+    """Storage type of a code (aqlm.py:20-29); a 4-bit code still takes an int8."""
+    for limit, dt in ((8, torch.int8), (16, torch.int16), (32, torch.int32), (64, torch.int64)):
+        if nbits <= limit:
+            return dt
+    raise ValueError(f"No dtype available for {nbits}-bit codebooks")
+
+
+@register_quantization_config("pq")
+class PQConfig(QuantizationConfig):
+    """Config class for PQ (AQLM-format) checkpoints.  aqlm.py:159-217."""
+
+    def __init__(self, in_group_size: int, nbits_per_codebook: int, num_codebooks: int,
+                 out_group_size: int = 1) -> None:
+        super().__init__()
+        self.in_group_size = in_group_size
+        self.nbits_per_codebook = nbits_per_codebook
+        self.num_codebooks = num_codebooks
+        self.out_group_size = out_group_size
+        assert self.out_group_size == 1                      # aqlm.py:178-179
+        if nbits_per_codebook > 16:
+            raise ValueError("PQ kernels support at most 16 bits per code")
+        self.pack_factor = self.in_group_size * self.out_group_size
+
+    def __repr__(self) -> str:
+        return (f"PQConfig(in_group_size={self.in_group_size}, "
+                f"nbits_per_codebook={self.nbits_per_codebook}, "
+                f"num_codebooks={self.num_codebooks}, "
+                f"out_group_size={self.out_group_size})")
+
+    @classmethod
+    def get_name(cls) -> str:
+        return "pq"
+
+    @classmethod
+    def get_supported_act_dtypes(cls) -> List[torch.dtype]:
+        return [torch.half, torch.bfloat16]
+
+    @classmethod
+    def get_min_capability(cls) -> int:
+        return 100                                           # sm_100a only
+
+    @classmethod
+    def get_config_filenames(cls) -> List[str]:
+        return []
+
+    @classmethod
+    def from_config(cls, config: Dict[str, Any]) -> "PQConfig":
+        return cls(cls.get_from_keys(config, ["in_group_size"]),
+                   cls.get_from_keys(config, ["nbits_per_codebook"]),
+                   cls.get_from_keys(config, ["num_codebooks"]),
+                   cls.get_from_keys(config, ["out_group_size"]))
+
+    @classmethod
+    def override_quantization_method(cls, hf_quant_cfg, user_quant) -> Optional[str]:
+        # An AQLM checkpoint can be served by this method when the user asks for it.
+        if user_quant == "pq" and hf_quant_cfg.get("quant_method") in ("aqlm", "pq"):
+            return "pq"
+        return None
+
+    def get_quant_method(self, layer: torch.nn.Module, prefix: str) -> Optional["PQLinearMethod"]:
+        from .linear import is_linear_layer
+        if is_linear_layer(layer):
+            return PQLinearMethod(self)
+        return None                                          # embeddings / lm_head stay dense
+
+
+class PQLinearMethod(LinearMethodBase):
+    """Linear method for PQ.  aqlm.py:220-374."""
+
+    def __init__(self, quant_config: PQConfig):
+        self.quant_config = quant_config
+
+    def create_weights(self, layer: torch.nn.Module, input_size_per_partition: int,
+                       output_partition_sizes: List[int], input_size: int, output_size: int,
+                       params_dtype: torch.dtype, **extra_weight_attrs):
+        del output_size, input_size
+        cfg = self.quant_config
+        if params_dtype not in (torch.half, torch.bfloat16):
+            raise ValueError("Only half and bfloat16 are currently supported by pq")
+        if input_size_per_partition % cfg.in_group_size != 0:
+            raise ValueError("The input size is not aligned with the quantized weight shape. "
+                             "This can be caused by too large tensor parallel size.")
+        output_size_per_partition = sum(output_partition_sizes)
+        if output_size_per_partition % cfg.out_group_size != 0:
+            raise ValueError("The output size is not aligned with the quantized weight shape. "
+                             "This can be caused by too large tensor parallel size.")
+
+        codes = Parameter(torch.empty(output_size_per_partition,
+                                      input_size_per_partition // cfg.pack_factor,
+                                      cfg.num_codebooks,
+                                      dtype=get_int_dtype(cfg.nbits_per_codebook)),
+                          requires_grad=False)
+        set_weight_attrs(codes, {"input_dim": 1, "output_dim": 0, "packed_dim": 1,
+                                 "pack_factor": cfg.pack_factor})
+
+        codebooks = Parameter(torch.empty(cfg.num_codebooks * len(output_partition_sizes),
+                                          2**cfg.nbits_per_codebook, cfg.out_group_size,
+                                          cfg.in_group_size, dtype=params_dtype),
+                              requires_grad=False)
+        # metadata: fixed size, concatenated along dim 0 by the fused-layer loaders
+        set_weight_attrs(codebooks, {"is_metadata": True,
+                                     "output_partition_sizes": output_partition_sizes})
+
+        scales = Parameter(torch.empty((output_size_per_partition // cfg.out_group_size, 1, 1, 1),
+                                       dtype=params_dtype),
+                           requires_grad=False)
+        set_weight_attrs(scales, {"output_dim": 0, "packed_dim": 0,
+                                  "pack_factor": cfg.out_group_size})
+
+        for name, p in (("codes", codes), ("codebooks", codebooks), ("scales", scales)):
+            layer.register_parameter(name, p)
+            set_weight_attrs(p, extra_weight_attrs)
+
+    def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
+        # The kernels read the checkpoint layout directly; nothing to repack. Make the
+        # contiguity the op requires explicit once, instead of per call.
+        for name in ("codes", "codebooks", "scales"):
+            p = getattr(layer, name)
+            if not p.data.is_contiguous():
+                p.data = p.data.contiguous()
+
+    def apply(self, layer: torch.nn.Module, x: torch.Tensor,
+              bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        codebooks = layer.codebooks
+        output_partition_sizes = getattr(codebooks, "output_partition_sizes", [])
+        # One op for every token count and format: the C side picks GEMV (decode) or the
+        # tcgen05 GEMM (prefill). Reference dispatch for comparison: aqlm.py:344-374.
+        return ops.pq_gemm(x, layer.codes, codebooks, layer.scales,
+                           list(output_partition_sizes), bias)
+
+    def dequantize(self, layer: torch.nn.Module, scaled: bool = True) -> torch.Tensor:
+        """Dense [N, K] weight (aqlm.py:37-74); bit-exact with the reference."""
+        codebooks = layer.codebooks
+        parts = list(getattr(codebooks, "output_partition_sizes", []))
+        return ops.pq_dequant(layer.codes, codebooks, parts, layer.scales if scaled else None)
