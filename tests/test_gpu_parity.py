@@ -97,6 +97,13 @@ def test_gemm_sweep(fmt, dtype, t):
     check_output(y, c)
     yd = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_DIRECT)
     check_output(yd, c, "direct")
+    n = sum(parts)
+    if _lib.load().pq_b200_workspace_bytes(_lib.ALGO_GEMV_LUT, t, n, k, d, b, m, len(parts)) > 0:
+        yl = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT)
+        check_output(yl, c, "lut")
+        # split-K partials are summed in a fixed order: the result is reproducible bit for bit
+        yl2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT)
+        assert torch.equal(yl, yl2)
 
 
 @pytest.mark.parametrize("shape", [
@@ -196,6 +203,12 @@ def test_full_size_properties(layer, fmt):
     ref = (g["x"].double() @ (w.double() * g["scales"].double().view(n, 1)).t())
     rms = float(((y.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()))
     assert rms < 2e-3, rms
+    for algo in (_lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT):
+        if algo == _lib.ALGO_GEMV_LUT and b > 8:
+            continue
+        ya = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, None, algo=algo)
+        rms = float(((ya.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()))
+        assert rms < 2e-3, (algo, rms)
     assert torch.isfinite(ws).all()
     # (4) linearity in x: f(2x) == 2 f(x) exactly (power-of-two scaling commutes with rounding)
     y2 = P.ops.pq_gemm(g["x"] * 2, g["codes"], g["codebooks"], g["scales"], parts, None)

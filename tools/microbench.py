@@ -41,15 +41,28 @@ def make(parts, k, b, d, m, dtype, nrep):
     return sets
 
 
-def time_loop(fn, sets, iters):
+def time_loop(fn, sets, iters, graph=True):
+    """One CUDA graph holding one call per weight set; replayed `iters` times between events."""
     for s in sets[:2]:
         fn(s)
+    torch.cuda.synchronize()
+    if graph:
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=st):
+                keep = [fn(s) for s in sets]
+        run = g.replay
+    else:
+        def run():
+            for s in sets:
+                fn(s)
+    run()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        for s in sets:
-            fn(s)
+        run()
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) * 1e-3 / (iters * len(sets))

@@ -13,6 +13,7 @@ int gemv_lut_dispatch(const void*, int64_t, const void*, const void*, const void
                       int, int, void*, int64_t, cudaStream_t);
 int64_t gemv_lut_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemv_lut_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+bool gemv_lut_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
                      void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
                      int, int, void*, int64_t, cudaStream_t);
@@ -72,7 +73,7 @@ int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales
 
 int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
   if (t > 8 && pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMM_TC;
-  if (pq::gemv_lut_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
+  if (pq::gemv_lut_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
   return PQ_ALGO_GEMV_DIRECT;
 }
 
