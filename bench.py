@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""bench.py - Llama-2-7B PQ decode step (all PQ linears) on N GPUs of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--format 8x8x1]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference        # the reference's torch PQ path on the host cores
+
+A step = one pass of a batch of B tokens through the 4 PQ linears of all 32 layers
+(qkv -> o -> gate_up -> down, TP = N: column-parallel QKV / gate-up, row-parallel O / down,
+one all-reduce after each row-parallel layer).  Weights are synthetic (uniform random codes,
+Gaussian codebooks) in the checkpoint layout; every layer has its own weights, so one step
+streams the whole model (0.81 GB at 1 bit/weight) - far more than the 126 MB L2.
+
+Printed JSON (rank 0): metric/value = tokens/s with inputs resident in HBM (CUDA-graph replay,
+CUDA events, max over ranks); e2e = the same through host buffers (pinned x -> H2D -> step ->
+D2H of the result, every step); roofline = the dominant kernel's algorithmic bytes / its
+measured launch time against the measured HBM peak; cpu_baseline = the oracle's restatement of
+the reference's generic_dequantize_gemm (same torch ops) on the host cores, bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+METRIC = "llama2_7b_pq_decode_tokens_per_s"
+UNIT = "tokens/s"
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as fh:
+            p = json.load(fh)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def parse_format(s: str):
+    b, d, m = (int(v) for v in s.split("x"))
+    return b, d, m
+
+
+# ------------------------------------------------------------------------------------------
+# clocks during the timed region
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index: int):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._h = None
+        self._thr = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self._nv.nvmlDeviceGetClockInfo(self._h, self._nv.NVML_CLOCK_SM))
+                mask = self._nv.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+                for bit, name in self.REASONS.items():
+                    if mask & bit and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        if self._h is not None:
+            self._thr.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._h is not None:
+            self._thr.join(timeout=1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the reference's torch PQ dequant+matmul on the host cores
+# ------------------------------------------------------------------------------------------
+def cpu_layer_time(fmt, batch, dtype, repeats, n_layers_total=32):
+    """One decoder layer's four PQ linears through the oracle's literal restatement of
+    generic_dequantize_gemm (aqlm.py:94-127: unpack -> embedding_bag -> scale -> F.linear).
+    Returns seconds per layer (best of `repeats` after one warm-up)."""
+    from oracle import pq_oracle as O
+    b, d, m = fmt
+    torch.set_num_threads(os.cpu_count() or 1)
+    shapes = [([4096] * 3, 4096), ([4096], 4096), ([11008] * 2, 4096), ([4096], 11008)]
+    cases = [O.make_case(parts, k, b, d, m, t=batch, dtype=dtype, seed=i) for i, (parts, k) in enumerate(shapes)]
+
+    def run():
+        for c in cases:
+            O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"],
+                                      c["partition_sizes"], None, literal=True)
+    run()
+    times = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        run()
+        times.append(time.perf_counter() - t0)
+    return min(times), statistics.median(times)
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    fmt = parse_format(args.format)
+    dtype = torch.float16 if args.dtype == "fp16" else torch.bfloat16
+    layers = 32
+    # W warm-up + K timed steps, each step = one decoder layer's linears (1/32 of the workload)
+    best, med = cpu_layer_time(fmt, args.batch, dtype, repeats=max(1, min(args.steps, 5)))
+    step_s = med * layers
+    value = args.batch / step_s
+    cores = torch.get_num_threads()
+    sample = (f"1 of {layers} decoder layers (qkv,o,gate_up,down) per step, x{layers} extrapolated; "
+              f"oracle port of aqlm.py:94-127 (unpack, embedding_bag, scale, F.linear), {args.dtype}")
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
+        "data": "synthetic",
+        "config": {"workload": "llama-2-7b all PQ linears, decode", "batch": args.batch,
+                   "format": args.format, "layers": layers},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+def capture(fn, stream):
+    with torch.cuda.stream(stream):
+        fn()
+        fn()
+        stream.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            out = fn()
+    return g, out
+
+
+def time_replays(run, steps, world, device):
+    """Exactly `steps` runs between events, barrier + synchronize on both sides, max over ranks."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()) / steps
+
+
+def run_gpu_arm(args):
+    import vllm_pq_b200 as P
+    from vllm_pq_b200 import stack as S
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+        P.init_tensor_parallel()
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+
+    fmt = parse_format(args.format)
+    b, d, m = fmt
+    dtype = torch.float16 if args.dtype == "fp16" else torch.bfloat16
+    P.ops.set_pdl(bool(args.pdl))
+    shape = S.SHAPES[args.model]
+    cfg = P.PQConfig(d, b, m, 1)
+    with torch.device(device):
+        model = S.PQLlamaLinearStack(shape, cfg, dtype).init_synthetic(seed=rank)
+    B = args.batch
+    stream = torch.cuda.Stream()
+
+    x_host = torch.randn(B, shape.hidden, dtype=dtype).pin_memory()
+    y_host = torch.empty(B, shape.hidden, dtype=dtype).pin_memory()
+    x_dev = x_host.to(device)
+
+    with torch.no_grad():
+        graph, y_dev = capture(lambda: model(x_dev), stream)
+
+        # per-projection graphs: the same kernel over all layers' weights (cold L2), for the roofline
+        kernel_rows = []
+        if rank == 0 or world > 1:
+            for name in ("qkv_proj", "o_proj", "gate_up_proj", "down_proj"):
+                lins = [getattr(layer, name) for layer in model.layers]
+                k_in = lins[0].codes.shape[1] * d
+                xin = torch.randn(B, k_in, dtype=dtype, device=device)
+                g_k, _ = capture(lambda: [lin.quant_method.apply(lin, xin) for lin in lins], stream)
+                kernel_rows.append((name, lins[0], g_k, len(lins)))
+
+    def step_resident():
+        with torch.cuda.stream(stream):
+            graph.replay()
+
+    def step_e2e():
+        with torch.cuda.stream(stream):
+            x_dev.copy_(x_host, non_blocking=True)
+            graph.replay()
+            y_host.copy_(y_dev, non_blocking=True)
+
+    def timed(run, steps):
+        # events must be recorded on the launching stream
+        with torch.cuda.stream(stream):
+            return time_replays(run, steps, world, device)
+
+    for _ in range(max(args.warmup, 3)):
+        step_e2e()
+    t_warm = time.time() + 0.5                    # let clocks settle on a fresh box
+    while time.time() < t_warm:
+        step_resident()
+    torch.cuda.synchronize()
+
+    with ClockSampler(local) as clk:
+        ms_step = timed(step_resident, args.steps)
+        ms_e2e = timed(step_e2e, args.steps)
+        kernels = {}
+        hbm_gbs, peak_src = measured_peaks()
+        for name, lin, g_k, n_l in kernel_rows:
+            ms_k = timed(lambda: g_k.replay(), max(10, args.steps // 4)) / n_l
+            ab = S.algorithmic_bytes(lin, B)
+            kernels[name] = {"us": ms_k * 1e3, "algorithmic_bytes": ab, "gbs": ab / (ms_k * 1e-3) / 1e9}
+    clocks = clk.summary()
+
+    if rank == 0:
+        dom = max(kernels, key=lambda k: kernels[k]["us"])
+        tot_us = sum(v["us"] for v in kernels.values())
+        for v in kernels.values():
+            v["share_of_step"] = v["us"] / tot_us
+        achieved = kernels[dom]["gbs"]
+        out = {
+            "metric": METRIC, "value": B / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16" if dtype == torch.float16 else "bf16",
+            "data": "synthetic",
+            "config": {"workload": f"{shape.name} all PQ linears ({len(model.layers)} layers x qkv,o,gate_up,down), decode",
+                       "batch": B, "format": f"{b}bit x d{d} x M{m}", "parallelism": f"tp{world}",
+                       "cold_l2": f"each step streams {model.code_bytes() * world / 1e6:.0f} MB of distinct codes (> 126 MB L2)",
+                       "launch": "CUDA graph" + (" + programmatic dependent launch" if args.pdl else ""),
+                       "allreduce": ("one-shot NVLink P2P kernel" if (world > 1 and P.distributed.oneshot_enabled())
+                                     else ("nccl" if world > 1 else "none"))},
+            "e2e": {"value": B / (ms_e2e * 1e-3), "unit": UNIT,
+                    "h2d_bytes_per_step": x_host.numel() * x_host.element_size(),
+                    "d2h_bytes_per_step": y_host.numel() * y_host.element_size()},
+            "gpu_launches": model.launches_per_step() * args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": peak_src,
+                         "whole_step_gbs": sum(v["algorithmic_bytes"] for v in kernels.values()) * len(model.layers)
+                         / (ms_step * 1e-3) / 1e9},
+            "kernels": kernels,
+        }
+        if world == 1 and not args.no_cpu:
+            best, med = cpu_layer_time(fmt, B, dtype, repeats=3)
+            out["cpu_baseline"] = {
+                "value": B / (med * shape.layers), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                "sample": f"1 of {shape.layers} decoder layers timed (best {best * 1e3:.0f} ms, median {med * 1e3:.0f} ms), "
+                          f"x{shape.layers}; oracle port of aqlm.py:94-127 with the reference's torch ops"}
+        print(json.dumps(out))
+    if world > 1:
+        P.destroy_tensor_parallel()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--format", default="8x8x1", help="nbits x d x M; 8x8x1 is BASELINE config 1's format")
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
+    ap.add_argument("--model", default="llama-2-7b")
+    ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

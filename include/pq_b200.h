@@ -79,7 +79,10 @@ PQ_API int pq_b200_dequant(const void* codes, const void* codebooks, const void*
                     void* w_out, int64_t n, int64_t k, int d, int nbits, int m,
                     const int64_t* part_sizes, int n_parts, int dtype, void* stream);
 
-/* Workspace (bytes) pq_b200_gemm needs for this problem with `algo`. */
+/* Workspace (bytes) pq_b200_gemm needs for this problem with `algo`.  The first 64 KiB of a
+ * non-empty workspace hold split-K ticket counters: they must be ZERO before the first call and
+ * every call leaves them zero, so one zero-initialised buffer can be reused for all calls that
+ * are ordered on a stream (the rest of the workspace is scratch).  256-byte aligned. */
 PQ_API int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d,
                                 int nbits, int m, int n_parts);
 

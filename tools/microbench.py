@@ -12,6 +12,18 @@ import vllm_pq_b200 as P  # noqa: E402
 from vllm_pq_b200 import _lib  # noqa: E402
 
 HBM_GBS = 6524.6
+
+try:
+    import pynvml
+    pynvml.nvmlInit()
+    _H = pynvml.nvmlDeviceGetHandleByIndex(0)
+
+    def sm_clock():
+        return pynvml.nvmlDeviceGetClockInfo(_H, pynvml.NVML_CLOCK_SM)
+except Exception:  # pragma: no cover
+    def sm_clock():
+        return -1
+
 SHAPES = {
     "sq4096": ([4096], 4096),
     "qkv7b": ([4096] * 3, 4096),
@@ -57,15 +69,23 @@ def time_loop(fn, sets, iters, graph=True):
         def run():
             for s in sets:
                 fn(s)
-    run()
+    import time
+    t_end = time.time() + WARM_S          # let the SM clock ramp up before timing
+    while time.time() < t_end:
+        run()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
         run()
     e1.record()
+    clk = sm_clock()
     torch.cuda.synchronize()
+    time_loop.last_clock = clk
     return e0.elapsed_time(e1) * 1e-3 / (iters * len(sets))
+
+
+WARM_S = 0.3
 
 
 def main():
@@ -78,9 +98,14 @@ def main():
     ap.add_argument("--pdl", type=int, default=0)
     ap.add_argument("--dequant", type=int, default=1)
     ap.add_argument("--out", default="")
+    ap.add_argument("--graph", type=int, default=1)
+    ap.add_argument("--warm", type=float, default=0.3)
+    ap.add_argument("--nrep", type=int, default=0)
     a = ap.parse_args()
     dtype = torch.float16 if a.dtype == "fp16" else torch.bfloat16
     P.ops.set_pdl(bool(a.pdl))
+    global WARM_S
+    WARM_S = a.warm
     names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3}
     rows = []
     for sname in a.shapes.split(","):
@@ -89,7 +114,7 @@ def main():
         for f in a.formats.split(","):
             b, d, m = (int(v) for v in f.split("x"))
             code_bytes = n * (k // d) * m * (1 if b <= 8 else 2)
-            nrep = max(2, min(64, (256 << 20) // code_bytes + 1))
+            nrep = a.nrep or max(2, min(64, (256 << 20) // code_bytes + 1))
             sets = make(parts, k, b, d, m, dtype, nrep)
             if a.dequant:
                 out_bytes = n * k * 2
@@ -102,14 +127,14 @@ def main():
                 for an in a.algos.split(","):
                     algo = names[an]
                     try:
-                        dt = time_loop(lambda s: P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=algo), sets, 5)
+                        dt = time_loop(lambda s: P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=algo), sets, 20, graph=bool(a.graph))
                     except RuntimeError as exc:
                         print(f"skip {sname} {f} t={t} {an}: {exc}")
                         continue
                     ab = algo_bytes(t, n, k, d, b, m, len(parts))
                     rows.append(dict(shape=sname, fmt=f, op="gemm", algo=an, t=t, us=dt * 1e6,
                                      gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
-                                     tflops=2 * t * n * k / dt / 1e12))
+                                     tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
                     print(rows[-1], flush=True)
             del sets
             torch.cuda.empty_cache()

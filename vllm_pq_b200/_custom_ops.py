@@ -34,6 +34,23 @@ _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes) -> Tensor")
 
 
+# One persistent, zero-initialised workspace per device.  The split-K kernels keep ticket
+# counters in its first 64 KiB and leave them zero (include/pq_b200.h), so it is zeroed only
+# when (re)allocated; reusing it also keeps allocator traffic off the decode path.
+_WORKSPACES = {}
+
+
+def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
+    ws = _WORKSPACES.get(device)
+    if ws is not None and ws.numel() >= nbytes:
+        return ws
+    size = max(int(nbytes) * 2, 32 << 20)
+    new = torch.zeros(size, dtype=torch.uint8, device=device)
+    if not torch.cuda.is_current_stream_capturing():
+        _WORKSPACES[device] = new        # a buffer born inside a graph capture lives in the graph's pool
+    return new
+
+
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
@@ -108,7 +125,7 @@ def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo):
         if algo == _lib.ALGO_AUTO:
             algo = lib.pq_b200_pick_algo(t, n, k, d, nbits, m)
         ws_bytes = lib.pq_b200_workspace_bytes(algo, t, n, k, d, nbits, m, np_)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=input.device) if ws_bytes else None
+        ws = _workspace(input.device, ws_bytes) if ws_bytes else None
         rc = lib.pq_b200_gemm(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
                               scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
                               arr, np_, _DTYPES[dt], algo, _ptr(ws), ws_bytes,

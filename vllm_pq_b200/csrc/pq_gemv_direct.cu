@@ -322,7 +322,13 @@ static int launch_maybe_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaS
 template <typename T, int D, typename CodeT, int M, int TT>
 static int launch_fast(GvArgs& a, int cbm, size_t smem, dim3 grid, cudaStream_t stream) {
   auto set = [&](auto kern) {
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static bool attr_set[64] = {};                 // per instantiation (lambda per kern type), per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (smem > 48 * 1024 && !attr_set[dev & 63]) {
+      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+      attr_set[dev & 63] = true;
+    }
     return launch_maybe_pdl(kern, grid, dim3(kGvThreads), smem, stream, a);
   };
   if (cbm == CB_SMEM_REPL) return set(pq_gemv_direct_kernel<T, D, CodeT, M, TT, CB_SMEM_REPL>);
@@ -354,7 +360,7 @@ static int gemv_direct_t(GvArgs& a, int d, int m, cudaStream_t stream,
   // token tile: as many tokens per pass as shared memory allows (<= 4)
   int tt = a.T >= 4 ? 4 : (a.T >= 2 ? 2 : 1);
   const int rows_gran = fast ? kGvWarps * kGvRB : kGvWarps;
-  int rows_per_cta = (int)(((int64_t)a.N + (int64_t)sms * 4 - 1) / ((int64_t)sms * 4));
+  int rows_per_cta = (int)(((int64_t)a.N + (int64_t)sms * 8 - 1) / ((int64_t)sms * 8));
   rows_per_cta = (rows_per_cta + rows_gran - 1) / rows_gran * rows_gran;
   a.rows_per_cta = rows_per_cta;
   int rc = make_parts(a.parts, part_sizes, n_parts, a.N, rows_per_cta);
@@ -379,7 +385,7 @@ static int gemv_direct_t(GvArgs& a, int d, int m, cudaStream_t stream,
   else { cbm = CB_GLOBAL; cb_smem = 0; }
   while (tt > 1 && cb_smem + (size_t)tt * a.xs_stride > 200 * 1024) tt >>= 1;
   const size_t smem = cb_smem + (size_t)tt * a.xs_stride;
-  if (smem > 227 * 1024) return PQ_ERR_UNSUPPORTED;
+  if (smem > 216 * 1024) return PQ_ERR_UNSUPPORTED;
   dim3 grid(a.parts.cta_end[n_parts - 1], (a.T + tt - 1) / tt);
 
 #define PQ_DISPATCH_D(CT, MM)                                                           \
