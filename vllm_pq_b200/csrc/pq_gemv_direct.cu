@@ -322,12 +322,15 @@ static int launch_maybe_pdl(Kern kern, dim3 grid, dim3 block, size_t smem, cudaS
 template <typename T, int D, typename CodeT, int M, int TT>
 static int launch_fast(GvArgs& a, int cbm, size_t smem, dim3 grid, cudaStream_t stream) {
   auto set = [&](auto kern) {
-    static bool attr_set[64] = {};                 // per instantiation (lambda per kern type), per device
+    // all three kernels share one function-pointer TYPE, so the flag is keyed by the codebook
+    // mode explicitly (a static inside this generic lambda is one object for all of them)
+    static bool attr_set[3][64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (smem > 48 * 1024 && !attr_set[dev & 63]) {
-      cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
-      attr_set[dev & 63] = true;
+    if (smem > 48 * 1024 && !attr_set[cbm][dev & 63]) {
+      const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 216 * 1024);
+      if (e != cudaSuccess) return (int)e;
+      attr_set[cbm][dev & 63] = true;
     }
     return launch_maybe_pdl(kern, grid, dim3(kGvThreads), smem, stream, a);
   };
