@@ -313,7 +313,7 @@ def main():
     ap.add_argument("--format", default="8x8x1", help="nbits x d x M; 8x8x1 is BASELINE config 1's format")
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--model", default="llama-2-7b")
-    ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--pdl", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

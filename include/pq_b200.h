@@ -70,6 +70,14 @@ PQ_API int pq_b200_abi_version(void);
 PQ_API void pq_b200_set_pdl(int enabled);
 PQ_API const char* pq_b200_strerror(int code);
 
+/* Diagnostics (tools/trace_lut.py); not part of the reference boundary.
+ * set_trace: device buffer of 16 x u64 per CTA that the table GEMV fills with %globaltimer phase
+ * stamps (NULL = off, the default).  last_launch: {grid.x, grid.y, cluster size, smem bytes}.
+ * max_active_clusters: cudaOccupancyMaxActiveClusters for the table GEMV. */
+PQ_API void pq_b200_debug_set_trace(void* device_buffer);
+PQ_API void pq_b200_debug_last_launch(int* out4);
+PQ_API int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes);
+
 /* Unscaled (scales == NULL; what aqlm_dequant returns, gemm_kernels.cu:563-592) or
  * scaled (aqlm.py:70-72) weights w_out[n, k].  Sum over the m codebooks is
  * accumulated in fp32 in codebook order and rounded to nearest even once; the
@@ -96,6 +104,9 @@ PQ_API int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, cons
                  int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
                  const int64_t* part_sizes, int n_parts, int dtype, int algo,
                  void* workspace, int64_t workspace_bytes, void* stream);
+
+/* 1 if kernel family `algo` covers this problem, else 0 (PQ_ALGO_AUTO: always 1). */
+PQ_API int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 
 /* Which PQ_ALGO_* would PQ_ALGO_AUTO choose. */
 PQ_API int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);

@@ -55,10 +55,8 @@ def test_golden_gemm(name, algo):
     c = dev(G.load(name))
     lib = _lib.load()
     t, k, n = c["x"].shape[0], c["x"].shape[1], c["codes"].shape[0]
-    if algo == _lib.ALGO_GEMV_LUT and lib.pq_b200_workspace_bytes(algo, t, n, k, c["d"], c["nbits"], c["m"], 1) == 0:
-        pytest.skip("LUT kernel does not cover this format")
-    if algo == _lib.ALGO_GEMM_TC and lib.pq_b200_pick_algo(64, n, k, c["d"], c["nbits"], c["m"]) != _lib.ALGO_GEMM_TC:
-        pytest.skip("tensor-core kernel does not cover this format")
+    if not lib.pq_b200_algo_supported(algo, t, n, k, c["d"], c["nbits"], c["m"]):
+        pytest.skip(f"{_lib.ALGO_NAMES[algo]} kernel does not cover this format")
     y = P.ops.pq_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], c["partition_sizes"], c["bias"], algo=algo)
     assert y.shape == c["y"].shape and y.dtype == c["y"].dtype
     check_output(y, c, _lib.ALGO_NAMES[algo])
@@ -98,7 +96,7 @@ def test_gemm_sweep(fmt, dtype, t):
     yd = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_DIRECT)
     check_output(yd, c, "direct")
     n = sum(parts)
-    if _lib.load().pq_b200_workspace_bytes(_lib.ALGO_GEMV_LUT, t, n, k, d, b, m, len(parts)) > 0:
+    if _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMV_LUT, t, n, k, d, b, m):
         yl = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT)
         check_output(yl, c, "lut")
         # split-K partials are summed in a fixed order: the result is reproducible bit for bit

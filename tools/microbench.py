@@ -25,6 +25,7 @@ except Exception:  # pragma: no cover
         return -1
 
 SHAPES = {
+    "tiny": ([128], 512),
     "sq4096": ([4096], 4096),
     "qkv7b": ([4096] * 3, 4096),
     "o7b": ([4096], 4096),

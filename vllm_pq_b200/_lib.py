@@ -28,12 +28,16 @@ SIGNATURES = {
     "pq_b200_abi_version": (c_int, []),
     "pq_b200_set_pdl": (None, [c_int]),
     "pq_b200_strerror": (c_char_p, [c_int]),
+    "pq_b200_debug_set_trace": (None, [c_void_p]),
+    "pq_b200_debug_last_launch": (None, [ctypes.POINTER(c_int)]),
+    "pq_b200_debug_max_active_clusters": (c_int, [c_int, c_int]),
     "pq_b200_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
                                 c_int, c_int, _I64P, c_int, c_int, c_void_p]),
     "pq_b200_workspace_bytes": (c_int64, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int]),
     "pq_b200_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
                              c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "pq_b200_algo_supported": (c_int, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_pick_algo": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_allreduce_oneshot": (c_int, [c_void_p, c_void_p, c_int64, c_int, _VPP, _VPP, c_int, c_int,
                                           c_int64, c_void_p]),

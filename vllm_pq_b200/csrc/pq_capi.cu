@@ -22,6 +22,9 @@ bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m)
 int allreduce_oneshot_dispatch(const void*, void*, int64_t, int, void* const*, void* const*, int, int,
                                int64_t, cudaStream_t);
 extern bool g_use_pdl;
+extern unsigned long long* g_lut_trace;
+extern int g_lut_last_grid[4];
+int lut_max_active_clusters(int cs, int smem);
 }  // namespace pq
 
 static int check_format(int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
@@ -60,6 +63,12 @@ const char* pq_b200_strerror(int code) {
 
 void pq_b200_set_pdl(int enabled) { pq::g_use_pdl = enabled != 0; }
 
+void pq_b200_debug_set_trace(void* device_buffer) { pq::g_lut_trace = (unsigned long long*)device_buffer; }
+void pq_b200_debug_last_launch(int* out4) { for (int i = 0; i < 4; ++i) out4[i] = pq::g_lut_last_grid[i]; }
+int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes) {
+  return pq::lut_max_active_clusters(cluster_size, smem_bytes);
+}
+
 int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales, void* w_out,
                     int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
                     int n_parts, int dtype, void* stream) {
@@ -75,6 +84,16 @@ int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) 
   if (t > 8 && pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMM_TC;
   if (pq::gemv_lut_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
   return PQ_ALGO_GEMV_DIRECT;
+}
+
+int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  if (t < 1 || n < 1 || k < 1 || d < 1 || k % d || nbits < 1 || nbits > 16 || m < 1) return 0;
+  switch (algo) {
+    case PQ_ALGO_AUTO: case PQ_ALGO_GEMV_DIRECT: return 1;
+    case PQ_ALGO_GEMV_LUT: return pq::gemv_lut_supported(t, n, k, d, nbits, m) ? 1 : 0;
+    case PQ_ALGO_GEMM_TC: return pq::gemm_tc_supported(t, n, k, d, nbits, m) ? 1 : 0;
+    default: return 0;
+  }
 }
 
 int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
@@ -103,8 +122,6 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
                                       d, nbits, m, part_sizes, n_parts, dtype, s);
     case PQ_ALGO_GEMV_LUT:
       if (!pq::gemv_lut_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
-      if (workspace_bytes < pq::gemv_lut_workspace(t, n, k, d, nbits, m, n_parts) || !workspace)
-        return PQ_ERR_WORKSPACE;
       return pq::gemv_lut_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
     case PQ_ALGO_GEMM_TC:
