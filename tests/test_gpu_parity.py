@@ -104,6 +104,41 @@ def test_gemm_sweep(fmt, dtype, t):
         assert torch.equal(yl, yl2)
 
 
+TC_SWEEP = [(8, 8, 1), (8, 8, 2), (16, 8, 1), (4, 4, 1), (8, 16, 1), (12, 8, 1), (8, 8, 3), (12, 4, 2)]
+
+
+@pytest.mark.parametrize("fmt", TC_SWEEP)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("t", [9, 16, 40, 130, 257])
+def test_gemm_tc_sweep(fmt, dtype, t):
+    """tcgen05 GEMM (prefill / batched decode): ragged partitions (tiles clipped at partition ends),
+    token counts that are not multiples of the MMA N, bias on odd cases."""
+    b, d, m = fmt
+    parts, k = [128, 200, 72], 256
+    c = O.make_case(parts, k, b, d, m, t=t, dtype=dtype, seed=11 + t, bias=(t % 2 == 1))
+    g = dev(c)
+    assert _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMM_TC, t, sum(parts), k, d, b, m)
+    y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMM_TC)
+    check_output(y, c, "tc")
+    # the A operand is the bit-exact dequantised weight and accumulation is fp32 in a fixed order:
+    # the result is reproducible, and equals what PQ_ALGO_AUTO picks for this token count
+    y2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"])
+    assert torch.equal(y, y2)
+
+
+def test_gemm_tc_prefill_full_size():
+    """BASELINE config 3 shape class at reduced N (Llama-3-8B K, 2048 tokens): tolerance against a
+    dense fp64 GEMM over pq_dequant's own (bit-exact) weights."""
+    parts, k, t = [1024, 1024], 4096, 2048
+    c = O.make_case(parts, k, 8, 8, 1, t=t, dtype=torch.bfloat16, seed=3)
+    g = dev(c)
+    y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, None)
+    w = P.ops.pq_dequant(g["codes"], g["codebooks"], parts).double() * g["scales"].double().view(-1, 1)
+    ref = g["x"].double() @ w.t()
+    rms = float((y.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt())
+    assert rms < 1.6e-2 / 4, rms
+
+
 @pytest.mark.parametrize("shape", [
     # (parts, K) incl. rows whose code bytes are not a multiple of 16 (scalar fallback) and Llama TP=8 down
     ([37], 8 * 43), ([4096], 1376), ([48], 8 * 2), ([8, 8], 8 * 1), ([300, 4], 8 * 100)])

@@ -31,6 +31,8 @@ SHAPES = {
     "o7b": ([4096], 4096),
     "gateup7b": ([11008] * 2, 4096),
     "down7b": ([4096], 11008),
+    "gateup8b": ([14336] * 2, 4096),
+    "down8b": ([4096], 14336),
     "gateup70b": ([28672] * 2, 8192),
     "down70b": ([8192], 28672),
 }

@@ -1,9 +1,488 @@
-// placeholder - filled in below in this round
+// Prefill-path PQ GEMM on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a.
+//
+//   y[t, n] = scale[n] * sum_k x[t, k] * W[n, k] + bias[n],   W = codebook gather of `codes`
+//
+// Replaces aqlm_dequant + F.linear (+ the in-place scale) of optimized_dequantize_gemm
+// (reference vllm/model_executor/layers/quantization/aqlm.py:132-156 and
+// csrc/quantization/aqlm/gemm_kernels.cu:185-295,544-597): the dense weight never exists in
+// HBM.  A persistent, warp-specialised CTA per SM works on tiles of 128 weight rows x BN tokens:
+//   warp 0      TMA producer: x tile [BN tokens][64 k] bf16/fp16 -> shared memory (128-byte
+//               swizzle) with cp.async.bulk.tensor, completion on an mbarrier
+//   warps 4-7   dequant producers: one weight row per thread; per 64-wide k block they read
+//               the row's codes (8-16 B), gather the codewords (shared-memory codebooks, or L2
+//               for 65536-entry books), sum additive codebooks in fp32 with ONE rounding - the
+//               same bits pq_b200_dequant writes - and store them as the A operand in the
+//               K-major 128-byte-swizzled layout the UMMA descriptor describes (16-byte chunk c
+//               of row r at r*128 + ((c ^ (r & 7)) << 4)); fence.proxy.async, then mbarrier arrive
+//   warp 1      one thread issues tcgen05.mma (M = 128 weight rows, N = BN tokens, K = 16) with
+//               the fp32 accumulator in tensor memory; tcgen05.commit frees the stage / publishes
+//               the accumulator
+//   warps 8-11  epilogue: tcgen05.ld (lane = weight row, column = token), scale and bias in fp32,
+//               one rounding, stores of 32 consecutive outputs per token per warp
+// Two accumulator stages (2 x BN <= 512 TMEM columns) overlap the epilogue of one tile with the
+// main loop of the next.  Weight rows are the MMA M operand so that decode-sized token counts
+// (BN = 16..64) still fill the 128-lane datapath.
+#include <cuda.h>
+
+#include <type_traits>
+
 #include "pq_common.cuh"
+
 namespace pq {
-int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
-                     void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
-                     int, int, void*, int64_t, cudaStream_t) { return PQ_ERR_UNSUPPORTED; }
-int64_t gemm_tc_workspace(int64_t, int64_t, int64_t, int, int, int, int) { return 0; }
-bool gemm_tc_supported(int64_t, int64_t, int64_t, int, int, int) { return false; }
+
+constexpr int kTcThreads = 384;
+constexpr int kTcBM = 128;                 // weight rows per tile = UMMA M
+constexpr int kTcBK = 64;                  // k per stage: 128 bytes = one swizzle atom
+constexpr int kTcMaxStages = 8;
+constexpr int kTcABytes = kTcBM * kTcBK * 2;
+constexpr int kTcTmemCols = 512;
+
+struct TcArgs {
+  const void* codes; const void* codebooks; const void* scales; const void* bias; void* y;
+  long long y_stride;
+  int T, N, K, E, M;
+  int BN;                                  // tokens per tile (UMMA N), multiple of 16
+  int n_tok_tiles, n_row_tiles;
+  int stages;
+  int cb_smem_bytes;                       // 0: gather codewords from global memory (L2)
+  int row_code_bytes;                      // bytes of codes per weight row
+  Parts parts;                             // cta_end counts 128-row tiles
+};
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count));
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle, dense 8-row groups (1024 B apart): LBO = 1 (unused), SBO = 64,
+// descriptor version 1 (sm_100), layout type 2 (SWIZZLE_128B).  cute/arch/mma_sm100_desc.hpp.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3fffu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: fp32 accumulate, A and B K-major, M = 128, N = bn.
+__device__ __forceinline__ uint32_t umma_idesc(int bn, bool bf16) {
+  const uint32_t fmt = bf16 ? 1u : 0u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(kTcBM >> 4) << 24);
+}
+
+// ---- dequant producer helpers -----------------------------------------------------------------
+template <int D> struct TcCw { uint32_t w[D / 2]; };
+
+template <int D>
+__device__ __forceinline__ TcCw<D> tc_ld_cw(const unsigned char* p, bool in_smem) {
+  TcCw<D> v;
+  if constexpr (D == 4) {
+    uint2 q = in_smem ? *reinterpret_cast<const uint2*>(p) : ld_cg_8(p);
+    v.w[0] = q.x; v.w[1] = q.y;
+  } else {
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) {
+      uint4 q = in_smem ? reinterpret_cast<const uint4*>(p)[i] : ld_cg_16(reinterpret_cast<const uint4*>(p) + i);
+      v.w[4 * i] = q.x; v.w[4 * i + 1] = q.y; v.w[4 * i + 2] = q.z; v.w[4 * i + 3] = q.w;
+    }
+  }
+  return v;
+}
+
+// Store one group's D elements into the K-major 128B-swizzled A tile: row r, k offset g*D.
+template <int D>
+__device__ __forceinline__ void tc_st_group(uint32_t a_row, int r7, int g, const TcCw<D>& v) {
+  if constexpr (D == 8) {
+    asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a_row + (uint32_t)((g ^ r7) << 4)),
+                 "r"(v.w[0]), "r"(v.w[1]), "r"(v.w[2]), "r"(v.w[3]) : "memory");
+  } else if constexpr (D == 4) {
+    asm volatile("st.shared.v2.u32 [%0], {%1,%2};" :: "r"(a_row + (uint32_t)((((g >> 1) ^ r7) << 4) + ((g & 1) << 3))),
+                 "r"(v.w[0]), "r"(v.w[1]) : "memory");
+  } else {
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+      asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" :: "r"(a_row + (uint32_t)(((2 * g + h) ^ r7) << 4)),
+                   "r"(v.w[4 * h]), "r"(v.w[4 * h + 1]), "r"(v.w[4 * h + 2]), "r"(v.w[4 * h + 3]) : "memory");
+  }
+}
+
+// One weight row, one 64-wide k block: gather, sum the M codebooks (fp32, one RNE rounding - the
+// bits pq_b200_dequant produces), store.  `cp` points at this row's codes for the block.
+template <typename T, int D, typename CodeT>
+__device__ __forceinline__ void tc_dequant_block(uint32_t a_row, int r7, const CodeT* cp, int M, int E,
+                                                 const unsigned char* cb, bool cb_in_smem, bool valid) {
+  constexpr int GPB = kTcBK / D;                  // groups per k block
+  const uint32_t emask = (uint32_t)E - 1u;
+  if (!valid) {
+    TcCw<D> z;
+#pragma unroll
+    for (int j = 0; j < D / 2; ++j) z.w[j] = 0u;
+#pragma unroll
+    for (int g = 0; g < GPB; ++g) tc_st_group<D>(a_row, r7, g, z);
+    return;
+  }
+  if (M == 1) {
+    // all codes of the block in one or two vector loads
+    constexpr int NB = GPB * (int)sizeof(CodeT);   // bytes: 4, 8, 16 or 32
+    uint32_t cw32[NB / 4];
+    if constexpr (NB == 4) cw32[0] = __ldg(reinterpret_cast<const uint32_t*>(cp));
+    else if constexpr (NB == 8) { uint2 q = __ldg(reinterpret_cast<const uint2*>(cp)); cw32[0] = q.x; cw32[1] = q.y; }
+    else {
+#pragma unroll
+      for (int i = 0; i < NB / 16; ++i) {
+        uint4 q = __ldg(reinterpret_cast<const uint4*>(cp) + i);
+        cw32[4 * i] = q.x; cw32[4 * i + 1] = q.y; cw32[4 * i + 2] = q.z; cw32[4 * i + 3] = q.w;
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < GPB; ++g) {
+      uint32_t code;
+      if constexpr (sizeof(CodeT) == 1) code = (cw32[g >> 2] >> (8 * (g & 3))) & 0xffu;
+      else code = (cw32[g >> 1] >> (16 * (g & 1))) & 0xffffu;
+      code &= emask;
+      const TcCw<D> v = tc_ld_cw<D>(cb + (size_t)code * (D * 2), cb_in_smem);
+      tc_st_group<D>(a_row, r7, g, v);
+    }
+  } else {
+#pragma unroll 2
+    for (int g = 0; g < GPB; ++g) {
+      float acc[D];
+#pragma unroll
+      for (int j = 0; j < D; ++j) acc[j] = 0.f;
+      for (int m = 0; m < M; ++m) {
+        const uint32_t code = (uint32_t)cp[g * M + m] & emask;
+        const TcCw<D> v = tc_ld_cw<D>(cb + ((size_t)m * E + code) * (D * 2), cb_in_smem);
+#pragma unroll
+        for (int j = 0; j < D / 2; ++j) {
+          const float2 f = Traits<T>::to_f2(v.w[j]);
+          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+        }
+      }
+      TcCw<D> o;
+#pragma unroll
+      for (int j = 0; j < D / 2; ++j) o.w[j] = Traits<T>::pack(acc[2 * j], acc[2 * j + 1]);
+      tc_st_group<D>(a_row, r7, g, o);
+    }
+  }
+}
+
+// ---- the kernel ---------------------------------------------------------------------------------
+template <typename T, int D, typename CodeT>
+__global__ void __launch_bounds__(kTcThreads, 1)
+pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
+  extern __shared__ __align__(1024) unsigned char tc_smem[];
+  __shared__ __align__(8) uint64_t bars[3 * kTcMaxStages + 4];
+  __shared__ uint32_t tmem_base_s;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // dynamic shared memory: [A stages | B stages | codebooks], 1024-byte aligned tiles
+  const uint32_t smem0 = (tc_smem_u32(tc_smem) + 1023u) & ~1023u;
+  const uint32_t b_bytes = (uint32_t)a.BN * 128u;
+  const uint32_t a_base = smem0;
+  const uint32_t b_base = smem0 + (uint32_t)a.stages * kTcABytes;
+  unsigned char* cb_smem = tc_smem + (smem0 - tc_smem_u32(tc_smem)) + (size_t)a.stages * (kTcABytes + b_bytes);
+
+  const uint32_t bar0 = tc_smem_u32(bars);
+  auto full_a = [&](int s) { return bar0 + 8u * s; };
+  auto full_b = [&](int s) { return bar0 + 8u * (kTcMaxStages + s); };
+  auto empty = [&](int s) { return bar0 + 8u * (2 * kTcMaxStages + s); };
+  auto tmem_full = [&](int i) { return bar0 + 8u * (3 * kTcMaxStages + i); };
+  auto tmem_empty = [&](int i) { return bar0 + 8u * (3 * kTcMaxStages + 2 + i); };
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < a.stages; ++s) { mbar_init(full_a(s), 4); mbar_init(full_b(s), 1); mbar_init(empty(s), 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(tmem_full(i), 1); mbar_init(tmem_empty(i), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" :: "l"(&tmap_x) : "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                 :: "r"(tc_smem_u32(&tmem_base_s)), "n"(kTcTmemCols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  const int KB = a.K / kTcBK;
+  const int total_tiles = a.n_tok_tiles * a.n_row_tiles;
+
+  if (warp == 0) {
+    // ===== TMA producer: x tiles =====
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int tt = tile / a.n_row_tiles;
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(empty(s), ph ^ 1u);
+          mbar_arrive_expect_tx(full_b(s), b_bytes);
+          tma_load_2d(b_base + (uint32_t)s * b_bytes, &tmap_x, kb * kTcBK, tt * a.BN, full_b(s));
+          if (++s == a.stages) { s = 0; ph ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(a.BN, std::is_same<T, __nv_bfloat16>::value);
+      int s = 0; uint32_t ph = 0; int acc = 0; uint32_t acc_ph = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        mbar_wait(tmem_empty(acc), acc_ph ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)acc * 256u;
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_wait(full_a(s), ph);
+          mbar_wait(full_b(s), ph);
+          tc_fence_after();
+          const uint64_t ad = umma_desc_sw128(a_base + (uint32_t)s * kTcABytes);
+          const uint64_t bd = umma_desc_sw128(b_base + (uint32_t)s * b_bytes);
+#pragma unroll
+          for (int k = 0; k < kTcBK / 16; ++k)       // +32 bytes (2 x 16 B) per K = 16 step inside the swizzle atom
+            umma_f16(d_tmem, ad + (uint64_t)(2 * k), bd + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(empty(s));                     // frees the stage when these MMAs retire
+          if (++s == a.stages) { s = 0; ph ^= 1u; }
+        }
+        umma_commit(tmem_full(acc));                 // accumulator complete
+        if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===== dequant producers: one weight row per thread =====
+    const int r = threadIdx.x - 128;
+    const int r7 = r & 7;
+    const bool cb_in_smem = a.cb_smem_bytes > 0;
+    const size_t part_cb_bytes = (size_t)a.M * a.E * D * 2;
+    int cur_part = -1;
+    int s = 0; uint32_t ph = 0;
+    constexpr int CODES_PER_KB = kTcBK / D;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int rt = tile % a.n_row_tiles;
+      const RowBlock rb = locate_row_block(a.parts, rt, kTcBM);
+      const int row = rb.row0 + r;
+      const bool valid = row < rb.row1;
+      const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * part_cb_bytes;
+      if (cb_in_smem && rb.part != cur_part) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");       // everyone is done with the old books
+        for (int i = r; i < a.cb_smem_bytes / 16; i += 128)
+          reinterpret_cast<uint4*>(cb_smem)[i] = __ldg(reinterpret_cast<const uint4*>(cb_g) + i);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        cur_part = rb.part;
+      }
+      const unsigned char* cb = cb_in_smem ? cb_smem : cb_g;
+      const CodeT* crow = reinterpret_cast<const CodeT*>(
+          reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(valid ? row : rb.row0) * a.row_code_bytes);
+      for (int kb = 0; kb < KB; ++kb) {
+        mbar_wait(empty(s), ph ^ 1u);
+        const uint32_t a_row = a_base + (uint32_t)s * kTcABytes + (uint32_t)r * 128u;
+        tc_dequant_block<T, D, CodeT>(a_row, r7, crow + (size_t)kb * CODES_PER_KB * a.M, a.M, a.E, cb, cb_in_smem, valid);
+        fence_proxy_async();                         // generic-proxy stores -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(full_a(s));
+        if (++s == a.stages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp >= 8) {
+    // ===== epilogue: TMEM -> registers -> y =====
+    const int w = warp - 8;                          // == warp % 4: the TMEM lanes this warp may read
+    int acc = 0; uint32_t acc_ph = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int tt = tile / a.n_row_tiles, rt = tile % a.n_row_tiles;
+      const RowBlock rb = locate_row_block(a.parts, rt, kTcBM);
+      const int row = rb.row0 + 32 * w + lane;
+      const bool valid = row < rb.row1;
+      float sc = 0.f, bi = 0.f;
+      if (valid) {
+        sc = Traits<T>::to_f(reinterpret_cast<const T*>(a.scales)[row]);
+        if (a.bias) bi = Traits<T>::to_f(reinterpret_cast<const T*>(a.bias)[row]);
+      }
+      mbar_wait(tmem_full(acc), acc_ph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (uint32_t)acc * 256u + ((uint32_t)(32 * w) << 16);
+      T* yrow = reinterpret_cast<T*>(a.y) + row;
+      for (int c0 = 0; c0 < a.BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_x32(taddr + (uint32_t)c0, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int tok = tt * a.BN + c0 + j;
+          if (valid && c0 + j < a.BN && tok < a.T)
+            yrow[(size_t)tok * a.y_stride] = Traits<T>::from_f(fmaf(__uint_as_float(v[j]), sc, bi));
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tmem_empty(acc));
+      if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(kTcTmemCols) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+
+static PFN_tmapEncodeTiled tmap_encoder() {
+  static PFN_tmapEncodeTiled fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (PFN_tmapEncodeTiled)p;
+  }();
+  return fn;
+}
+
+// x [T, K] row-major (row stride x_stride elements) as a 2-D tensor map: box = 64 k x bn tokens,
+// 128-byte swizzle, out-of-bounds tokens read as zero.
+static int make_x_tmap(CUtensorMap* map, const void* x, int64_t x_stride, int64_t t, int64_t k, int bn, int dtype) {
+  PFN_tmapEncodeTiled enc = tmap_encoder();
+  if (!enc) return PQ_ERR_UNSUPPORTED;
+  const cuuint64_t gdim[2] = {(cuuint64_t)k, (cuuint64_t)t};
+  const cuuint64_t gstride[1] = {(cuuint64_t)x_stride * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)bn};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, dtype == PQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                         const_cast<void*>(x), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
+}
+
+struct TcPlan { int bn, n_tok_tiles, stages, cb_smem, smem_total; };
+
+static bool tc_plan(TcPlan& pl, int64_t t, int64_t k, int d, int nbits, int m) {
+  const int tok_tiles = (int)((t + 255) / 256);
+  int bn = (int)((t + tok_tiles - 1) / tok_tiles);
+  bn = (bn + 15) / 16 * 16;
+  pl.bn = bn;
+  pl.n_tok_tiles = (int)((t + bn - 1) / bn);
+  const int64_t cb = (int64_t)m * (1 << nbits) * d * 2;
+  pl.cb_smem = cb <= 64 * 1024 ? (int)cb : 0;
+  const int stage = kTcABytes + bn * 128;
+  int stages = (int)((225 * 1024 - 1024 - pl.cb_smem) / stage);
+  if (stages > kTcMaxStages) stages = kTcMaxStages;
+  if (stages > k / kTcBK) stages = (int)(k / kTcBK) < 2 ? 2 : (int)(k / kTcBK);
+  pl.stages = stages;
+  pl.smem_total = stages * stage + pl.cb_smem + 1024;
+  return stages >= 2;
+}
+
+bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  if (t < 1 || n < 1 || k < kTcBK || k % kTcBK) return false;      // whole 64-wide k blocks
+  if (d != 4 && d != 8 && d != 16) return false;
+  if (m < 1 || m > 8 || nbits < 1 || nbits > 16) return false;
+  TcPlan pl;
+  return tc_plan(pl, t, k, d, nbits, m);
+}
+
+int64_t gemm_tc_workspace(int64_t, int64_t, int64_t, int, int, int, int) { return 0; }
+
+template <typename T, int D, typename CodeT>
+static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, cudaStream_t stream) {
+  auto kern = pq_gemm_tc_kernel<T, D, CodeT>;
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[dev & 63] = true;
+  }
+  const int tiles = a.n_tok_tiles * a.n_row_tiles;
+  const int grid = tiles < sm_count() ? tiles : sm_count();
+  kern<<<grid, kTcThreads, pl.smem_total, stream>>>(map, a);
+  return (int)cudaGetLastError();
+}
+
+template <typename T, typename CodeT>
+static int launch_tc_d(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, int d, cudaStream_t stream) {
+  switch (d) {
+    case 4: return launch_tc<T, 4, CodeT>(map, a, pl, stream);
+    case 8: return launch_tc<T, 8, CodeT>(map, a, pl, stream);
+    default: return launch_tc<T, 16, CodeT>(map, a, pl, stream);
+  }
+}
+
+int gemm_tc_dispatch(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                     const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                     int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                     int n_parts, int dtype, void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
+  (void)workspace; (void)workspace_bytes;
+  if ((uintptr_t)x % 16 || (x_stride * 2) % 16 || (uintptr_t)codes % 16) return PQ_ERR_ALIGN;
+  TcPlan pl;
+  if (!tc_plan(pl, t, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  TcArgs a{};
+  a.codes = codes; a.codebooks = codebooks; a.scales = scales; a.bias = bias; a.y = y; a.y_stride = y_stride;
+  a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
+  a.BN = pl.bn; a.n_tok_tiles = pl.n_tok_tiles; a.stages = pl.stages; a.cb_smem_bytes = pl.cb_smem;
+  a.row_code_bytes = (int)(k / d * m * (nbits <= 8 ? 1 : 2));
+  int rc = make_parts(a.parts, part_sizes, n_parts, n, kTcBM);
+  if (rc) return rc;
+  a.n_row_tiles = a.parts.cta_end[n_parts - 1];
+  CUtensorMap map;
+  rc = make_x_tmap(&map, x, x_stride, t, k, pl.bn, dtype);
+  if (rc) return rc;
+  if (dtype == PQ_F16)
+    return nbits <= 8 ? launch_tc_d<__half, uint8_t>(map, a, pl, d, stream)
+                      : launch_tc_d<__half, uint16_t>(map, a, pl, d, stream);
+  return nbits <= 8 ? launch_tc_d<__nv_bfloat16, uint8_t>(map, a, pl, d, stream)
+                    : launch_tc_d<__nv_bfloat16, uint16_t>(map, a, pl, d, stream);
+}
+
+}  // namespace pq
