@@ -36,6 +36,8 @@ constexpr int kTcBK = 64;                  // k per stage: 128 bytes = one swizz
 constexpr int kTcMaxStages = 8;
 constexpr int kTcABytes = kTcBM * kTcBK * 2;
 constexpr int kTcTmemCols = 512;
+constexpr int kTcCodeRing = 4;             // 16..64-byte code chunks in flight per dequant thread
+constexpr int kTcRingVec = 128 * 16;       // one 16-byte vector per dequant thread
 
 struct TcArgs {
   const void* codes; const void* codebooks; const void* scales; const void* bias; void* y;
@@ -45,6 +47,7 @@ struct TcArgs {
   int n_tok_tiles, n_row_tiles;
   int stages;
   int cb_smem_bytes;                       // 0: gather codewords from global memory (L2)
+  int cb_stride;                           // bytes between codebook entries as staged (128 when replicated)
   int row_code_bytes;                      // bytes of codes per weight row
   Parts parts;                             // cta_end counts 128-row tiles
 };
@@ -118,17 +121,32 @@ __device__ __forceinline__ uint32_t umma_idesc(int bn, bool bf16) {
 // ---- dequant producer helpers -----------------------------------------------------------------
 template <int D> struct TcCw { uint32_t w[D / 2]; };
 
+// Codeword fetch: explicit shared-space vector loads (a generic pointer makes the compiler split the
+// 16-byte access into three narrower ones), or L2 (ld.global.cg) for books that do not fit.
 template <int D>
 __device__ __forceinline__ TcCw<D> tc_ld_cw(const unsigned char* p, bool in_smem) {
   TcCw<D> v;
-  if constexpr (D == 4) {
-    uint2 q = in_smem ? *reinterpret_cast<const uint2*>(p) : ld_cg_8(p);
-    v.w[0] = q.x; v.w[1] = q.y;
-  } else {
+  if (in_smem) {
+    const uint32_t sa = (uint32_t)__cvta_generic_to_shared(p);
+    if constexpr (D == 4) {
+      asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.w[0]), "=r"(v.w[1]) : "r"(sa));
+    } else {
 #pragma unroll
-    for (int i = 0; i < D / 8; ++i) {
-      uint4 q = in_smem ? reinterpret_cast<const uint4*>(p)[i] : ld_cg_16(reinterpret_cast<const uint4*>(p) + i);
-      v.w[4 * i] = q.x; v.w[4 * i + 1] = q.y; v.w[4 * i + 2] = q.z; v.w[4 * i + 3] = q.w;
+      for (int i = 0; i < D / 8; ++i)
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(v.w[4 * i]), "=r"(v.w[4 * i + 1]), "=r"(v.w[4 * i + 2]), "=r"(v.w[4 * i + 3])
+                     : "r"(sa + 16 * i));
+    }
+  } else {
+    if constexpr (D == 4) {
+      uint2 q = ld_cg_8(p);
+      v.w[0] = q.x; v.w[1] = q.y;
+    } else {
+#pragma unroll
+      for (int i = 0; i < D / 8; ++i) {
+        uint4 q = ld_cg_16(reinterpret_cast<const uint4*>(p) + i);
+        v.w[4 * i] = q.x; v.w[4 * i + 1] = q.y; v.w[4 * i + 2] = q.z; v.w[4 * i + 3] = q.w;
+      }
     }
   }
   return v;
@@ -151,68 +169,99 @@ __device__ __forceinline__ void tc_st_group(uint32_t a_row, int r7, int g, const
   }
 }
 
-// One weight row, one 64-wide k block: gather, sum the M codebooks (fp32, one RNE rounding - the
-// bits pq_b200_dequant produces), store.  `cp` points at this row's codes for the block.
-template <typename T, int D, typename CodeT>
-__device__ __forceinline__ void tc_dequant_block(uint32_t a_row, int r7, const CodeT* cp, int M, int E,
-                                                 const unsigned char* cb, bool cb_in_smem, bool valid) {
-  constexpr int GPB = kTcBK / D;                  // groups per k block
-  const uint32_t emask = (uint32_t)E - 1u;
-  if (!valid) {
-    TcCw<D> z;
+template <int D>
+__device__ __forceinline__ void tc_zero_block(uint32_t a_row, int r7) {
+  TcCw<D> z;
 #pragma unroll
-    for (int j = 0; j < D / 2; ++j) z.w[j] = 0u;
+  for (int j = 0; j < D / 2; ++j) z.w[j] = 0u;
 #pragma unroll
-    for (int g = 0; g < GPB; ++g) tc_st_group<D>(a_row, r7, g, z);
-    return;
+  for (int g = 0; g < kTcBK / D; ++g) tc_st_group<D>(a_row, r7, g, z);
+}
+
+template <typename CodeT>
+__device__ __forceinline__ uint32_t tc_code_at(const uint32_t* cw, int idx) {   // idx constant after unrolling
+  if constexpr (sizeof(CodeT) == 1) return (cw[idx >> 2] >> (8 * (idx & 3))) & 0xffu;
+  else return (cw[idx >> 1] >> (16 * (idx & 1))) & 0xffffu;
+}
+
+// Sum of the M codewords of one group in fp32 (codebook order), ONE RNE rounding: the bits
+// pq_b200_dequant produces.
+template <typename T, int D>
+__device__ __forceinline__ void tc_accumulate(float (&acc)[D], const TcCw<D>& v) {
+#pragma unroll
+  for (int j = 0; j < D / 2; ++j) {
+    const float2 f = Traits<T>::to_f2(v.w[j]);
+    acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
   }
-  if (M == 1) {
-    // all codes of the block in one or two vector loads
-    constexpr int NB = GPB * (int)sizeof(CodeT);   // bytes: 4, 8, 16 or 32
-    uint32_t cw32[NB / 4];
-    if constexpr (NB == 4) cw32[0] = __ldg(reinterpret_cast<const uint32_t*>(cp));
-    else if constexpr (NB == 8) { uint2 q = __ldg(reinterpret_cast<const uint2*>(cp)); cw32[0] = q.x; cw32[1] = q.y; }
-    else {
+}
+
+// One weight row, one 64-wide k block, the block's (64 / D) * M codes already in registers.
+template <typename T, int D, typename CodeT, int M>
+__device__ __forceinline__ void tc_dequant_regs(uint32_t a_row, int r7, const uint32_t* cw, int E,
+                                                const unsigned char* cb, uint32_t cb_stride, bool cb_in_smem) {
+  constexpr int GPB = kTcBK / D;
+  const uint32_t emask = (uint32_t)E - 1u;
+  // all gathers of a batch are issued before the first store: the loads overlap instead of each
+  // store waiting a full shared-memory round trip (the dominant stall in the first ncu capture)
+  constexpr int GB = (M == 1) ? (GPB < 8 ? GPB : 8) : (8 / M);      // groups per batch
 #pragma unroll
-      for (int i = 0; i < NB / 16; ++i) {
-        uint4 q = __ldg(reinterpret_cast<const uint4*>(cp) + i);
-        cw32[4 * i] = q.x; cw32[4 * i + 1] = q.y; cw32[4 * i + 2] = q.z; cw32[4 * i + 3] = q.w;
-      }
-    }
+  for (int g0 = 0; g0 < GPB; g0 += GB) {
+    TcCw<D> v[GB][M];
 #pragma unroll
-    for (int g = 0; g < GPB; ++g) {
-      uint32_t code;
-      if constexpr (sizeof(CodeT) == 1) code = (cw32[g >> 2] >> (8 * (g & 3))) & 0xffu;
-      else code = (cw32[g >> 1] >> (16 * (g & 1))) & 0xffffu;
-      code &= emask;
-      const TcCw<D> v = tc_ld_cw<D>(cb + (size_t)code * (D * 2), cb_in_smem);
-      tc_st_group<D>(a_row, r7, g, v);
-    }
-  } else {
-#pragma unroll 2
-    for (int g = 0; g < GPB; ++g) {
-      float acc[D];
+    for (int g = 0; g < GB; ++g)
 #pragma unroll
-      for (int j = 0; j < D; ++j) acc[j] = 0.f;
       for (int m = 0; m < M; ++m) {
-        const uint32_t code = (uint32_t)cp[g * M + m] & emask;
-        const TcCw<D> v = tc_ld_cw<D>(cb + ((size_t)m * E + code) * (D * 2), cb_in_smem);
-#pragma unroll
-        for (int j = 0; j < D / 2; ++j) {
-          const float2 f = Traits<T>::to_f2(v.w[j]);
-          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
-        }
+        const uint32_t code = tc_code_at<CodeT>(cw, (g0 + g) * M + m) & emask;
+        v[g][m] = tc_ld_cw<D>(cb + ((size_t)m * E + code) * cb_stride, cb_in_smem);
       }
-      TcCw<D> o;
 #pragma unroll
-      for (int j = 0; j < D / 2; ++j) o.w[j] = Traits<T>::pack(acc[2 * j], acc[2 * j + 1]);
-      tc_st_group<D>(a_row, r7, g, o);
+    for (int g = 0; g < GB; ++g) {
+      if constexpr (M == 1) {
+        tc_st_group<D>(a_row, r7, g0 + g, v[g][0]);
+      } else {
+        float acc[D];
+#pragma unroll
+        for (int j = 0; j < D; ++j) acc[j] = 0.f;
+#pragma unroll
+        for (int m = 0; m < M; ++m) tc_accumulate<T, D>(acc, v[g][m]);
+        TcCw<D> o;
+#pragma unroll
+        for (int j = 0; j < D / 2; ++j) o.w[j] = Traits<T>::pack(acc[2 * j], acc[2 * j + 1]);
+        tc_st_group<D>(a_row, r7, g0 + g, o);
+      }
     }
   }
 }
 
-// ---- the kernel ---------------------------------------------------------------------------------
+// Any M, codes read one by one from global memory (rows that are not 16-byte multiples, M = 3, ...).
 template <typename T, int D, typename CodeT>
+__device__ __forceinline__ void tc_dequant_generic(uint32_t a_row, int r7, const CodeT* cp, int M, int E,
+                                                   const unsigned char* cb, uint32_t cb_stride, bool cb_in_smem) {
+  constexpr int GPB = kTcBK / D;
+  const uint32_t emask = (uint32_t)E - 1u;
+#pragma unroll 2
+  for (int g = 0; g < GPB; ++g) {
+    float acc[D];
+#pragma unroll
+    for (int j = 0; j < D; ++j) acc[j] = 0.f;
+    TcCw<D> v;
+    for (int m = 0; m < M; ++m) {
+      const uint32_t code = (uint32_t)cp[g * M + m] & emask;
+      v = tc_ld_cw<D>(cb + ((size_t)m * E + code) * cb_stride, cb_in_smem);
+      tc_accumulate<T, D>(acc, v);
+    }
+    if (M > 1) {
+#pragma unroll
+      for (int j = 0; j < D / 2; ++j) v.w[j] = Traits<T>::pack(acc[2 * j], acc[2 * j + 1]);
+    }
+    tc_st_group<D>(a_row, r7, g, v);
+  }
+}
+
+// ---- the kernel ---------------------------------------------------------------------------------
+// MT: codebooks per group known at compile time (1, 2, 4: codes prefetched through a per-thread
+// cp.async ring) or 0 (any M, codes read from global memory as needed).
+template <typename T, int D, typename CodeT, int MT>
 __global__ void __launch_bounds__(kTcThreads, 1)
 pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
   extern __shared__ __align__(1024) unsigned char tc_smem[];
@@ -294,13 +343,56 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
     }
   } else if (warp >= 4 && warp < 8) {
     // ===== dequant producers: one weight row per thread =====
+    constexpr int GPB = kTcBK / D;
+    constexpr int CBYTES = MT > 0 ? GPB * MT * (int)sizeof(CodeT) : 16;   // code bytes per row and k block
+    constexpr int CHB = CBYTES > 16 ? CBYTES : 16;                         // ring chunk bytes per thread
+    constexpr int CH = CHB / CBYTES;                                       // k blocks per chunk
+    constexpr int NV = CHB / 16;
+    constexpr int NW = CBYTES / 4;
     const int r = threadIdx.x - 128;
     const int r7 = r & 7;
     const bool cb_in_smem = a.cb_smem_bytes > 0;
+    const uint32_t cb_stride = (uint32_t)a.cb_stride;
+    const int repl = a.cb_stride / (D * 2);          // copies of each entry in its 128-byte line (1: flat)
+    const uint32_t lane_off = (uint32_t)(lane & (repl - 1)) * (D * 2);
     const size_t part_cb_bytes = (size_t)a.M * a.E * D * 2;
+    const uint32_t ring0 = tc_smem_u32(cb_smem + a.cb_smem_bytes) + (uint32_t)r * 16u;
+    const int n_chunks = KB / CH;
     int cur_part = -1;
     int s = 0; uint32_t ph = 0;
-    constexpr int CODES_PER_KB = kTcBK / D;
+
+    // issue cursor of the code ring: runs kTcCodeRing chunks ahead of the consumer, across tiles
+    int itile = blockIdx.x, ichunk = 0, islot = 0;
+    const unsigned char* irow = nullptr;
+    auto seek = [&]() {
+      irow = nullptr;
+      if (itile < total_tiles) {
+        const RowBlock rb = locate_row_block(a.parts, itile % a.n_row_tiles, kTcBM);
+        if (rb.row0 + r < rb.row1)
+          irow = reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(rb.row0 + r) * a.row_code_bytes;
+      }
+    };
+    auto issue = [&]() {
+      if constexpr (MT > 0) {
+        if (itile < total_tiles) {
+          if (irow != nullptr) {
+#pragma unroll
+            for (int v = 0; v < NV; ++v)
+              asm volatile("cp.async.cg.shared.global [%0], [%1], 16;"
+                           :: "r"(ring0 + (uint32_t)((islot * NV + v) * kTcRingVec)),
+                              "l"(irow + (size_t)ichunk * CHB + 16 * v) : "memory");
+          }
+          if (++ichunk == n_chunks) { ichunk = 0; itile += gridDim.x; seek(); }
+          islot = (islot + 1 == kTcCodeRing) ? 0 : islot + 1;
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+      }
+    };
+    seek();
+#pragma unroll
+    for (int j = 0; j < kTcCodeRing; ++j) issue();
+    int cslot = 0;
+
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const int rt = tile % a.n_row_tiles;
       const RowBlock rb = locate_row_block(a.parts, rt, kTcBM);
@@ -309,22 +401,52 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
       const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * part_cb_bytes;
       if (cb_in_smem && rb.part != cur_part) {
         asm volatile("bar.sync 1, 128;" ::: "memory");       // everyone is done with the old books
-        for (int i = r; i < a.cb_smem_bytes / 16; i += 128)
-          reinterpret_cast<uint4*>(cb_smem)[i] = __ldg(reinterpret_cast<const uint4*>(cb_g) + i);
+        for (int e = r; e < a.M * a.E; e += 128) {           // entry e -> `repl` copies in its line
+          const TcCw<D> v = tc_ld_cw<D>(cb_g + (size_t)e * (D * 2), false);
+          for (int c = 0; c < repl; ++c) {
+            uint32_t* dst = reinterpret_cast<uint32_t*>(cb_smem + (size_t)e * cb_stride + c * (D * 2));
+#pragma unroll
+            for (int j = 0; j < D / 2; ++j) dst[j] = v.w[j];
+          }
+        }
         asm volatile("bar.sync 1, 128;" ::: "memory");
         cur_part = rb.part;
       }
-      const unsigned char* cb = cb_in_smem ? cb_smem : cb_g;
+      const unsigned char* cb = (cb_in_smem ? cb_smem : cb_g) + lane_off;
       const CodeT* crow = reinterpret_cast<const CodeT*>(
           reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(valid ? row : rb.row0) * a.row_code_bytes);
       for (int kb = 0; kb < KB; ++kb) {
+        uint32_t cw[NW];
+        if constexpr (MT > 0) {
+          const int sub = kb & (CH - 1);
+          if (sub == 0) asm volatile("cp.async.wait_group %0;" :: "n"(kTcCodeRing - 1) : "memory");
+          if (valid) {
+            if constexpr (CBYTES >= 16) {
+#pragma unroll
+              for (int v = 0; v < NV; ++v)
+                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                             : "=r"(cw[4 * v]), "=r"(cw[4 * v + 1]), "=r"(cw[4 * v + 2]), "=r"(cw[4 * v + 3])
+                             : "r"(ring0 + (uint32_t)((cslot * NV + v) * kTcRingVec)));
+            } else if constexpr (CBYTES == 8) {
+              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(cw[0]), "=r"(cw[1])
+                           : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 8)));
+            } else {
+              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cw[0]) : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 4)));
+            }
+          }
+        }
         mbar_wait(empty(s), ph ^ 1u);
         const uint32_t a_row = a_base + (uint32_t)s * kTcABytes + (uint32_t)r * 128u;
-        tc_dequant_block<T, D, CodeT>(a_row, r7, crow + (size_t)kb * CODES_PER_KB * a.M, a.M, a.E, cb, cb_in_smem, valid);
+        if (!valid) tc_zero_block<D>(a_row, r7);
+        else if constexpr (MT > 0) tc_dequant_regs<T, D, CodeT, (MT > 0 ? MT : 1)>(a_row, r7, cw, a.E, cb, cb_stride, cb_in_smem);
+        else tc_dequant_generic<T, D, CodeT>(a_row, r7, crow + (size_t)kb * GPB * a.M, a.M, a.E, cb, cb_stride, cb_in_smem);
         fence_proxy_async();                         // generic-proxy stores -> visible to the tensor core
         __syncwarp();
         if (lane == 0) mbar_arrive(full_a(s));
         if (++s == a.stages) { s = 0; ph ^= 1u; }
+        if constexpr (MT > 0) {
+          if ((kb & (CH - 1)) == CH - 1) { issue(); cslot = (cslot + 1 == kTcCodeRing) ? 0 : cslot + 1; }
+        }
       }
     }
   } else if (warp >= 8) {
@@ -404,7 +526,7 @@ static int make_x_tmap(CUtensorMap* map, const void* x, int64_t x_stride, int64_
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-struct TcPlan { int bn, n_tok_tiles, stages, cb_smem, smem_total; };
+struct TcPlan { int bn, n_tok_tiles, stages, cb_smem, cb_stride, mt, ring_bytes, smem_total; };
 
 static bool tc_plan(TcPlan& pl, int64_t t, int64_t k, int d, int nbits, int m) {
   const int tok_tiles = (int)((t + 255) / 256);
@@ -412,14 +534,24 @@ static bool tc_plan(TcPlan& pl, int64_t t, int64_t k, int d, int nbits, int m) {
   bn = (bn + 15) / 16 * 16;
   pl.bn = bn;
   pl.n_tok_tiles = (int)((t + bn - 1) / bn);
-  const int64_t cb = (int64_t)m * (1 << nbits) * d * 2;
-  pl.cb_smem = cb <= 64 * 1024 ? (int)cb : 0;
+  // codebooks: replicated to one 128-byte line per entry (conflict-free gathers) if that fits in
+  // 64 KiB, else flat in shared memory, else gathered from L2
+  const int64_t entries = (int64_t)m * (1 << nbits);
+  pl.cb_stride = d * 2; pl.cb_smem = 0;
+  if (entries * 128 <= 64 * 1024) { pl.cb_smem = (int)(entries * 128); pl.cb_stride = 128; }
+  else if (entries * d * 2 <= 64 * 1024) pl.cb_smem = (int)(entries * d * 2);
+  // code ring (compile-time M): rows must be whole 16-byte vectors
+  const int code_bytes = nbits <= 8 ? 1 : 2;
+  const int64_t row_bytes = k / d * m * code_bytes;
+  const int cbytes = kTcBK / d * m * code_bytes;
+  pl.mt = ((m == 1 || m == 2 || m == 4) && row_bytes % 16 == 0 && cbytes <= 64) ? m : 0;
+  pl.ring_bytes = pl.mt ? kTcCodeRing * (cbytes > 16 ? cbytes : 16) * 128 : 0;
   const int stage = kTcABytes + bn * 128;
-  int stages = (int)((225 * 1024 - 1024 - pl.cb_smem) / stage);
+  int stages = (int)((225 * 1024 - 1024 - pl.cb_smem - pl.ring_bytes) / stage);
   if (stages > kTcMaxStages) stages = kTcMaxStages;
   if (stages > k / kTcBK) stages = (int)(k / kTcBK) < 2 ? 2 : (int)(k / kTcBK);
   pl.stages = stages;
-  pl.smem_total = stages * stage + pl.cb_smem + 1024;
+  pl.smem_total = stages * stage + pl.cb_smem + pl.ring_bytes + 1024;
   return stages >= 2;
 }
 
@@ -433,9 +565,9 @@ bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m)
 
 int64_t gemm_tc_workspace(int64_t, int64_t, int64_t, int, int, int, int) { return 0; }
 
-template <typename T, int D, typename CodeT>
+template <typename T, int D, typename CodeT, int MT>
 static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, cudaStream_t stream) {
-  auto kern = pq_gemm_tc_kernel<T, D, CodeT>;
+  auto kern = pq_gemm_tc_kernel<T, D, CodeT, MT>;
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -452,11 +584,19 @@ static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, 
 
 template <typename T, typename CodeT>
 static int launch_tc_d(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, int d, cudaStream_t stream) {
-  switch (d) {
-    case 4: return launch_tc<T, 4, CodeT>(map, a, pl, stream);
-    case 8: return launch_tc<T, 8, CodeT>(map, a, pl, stream);
-    default: return launch_tc<T, 16, CodeT>(map, a, pl, stream);
+#define PQ_TC_MT(DD)                                                          \
+  switch (pl.mt) {                                                            \
+    case 1: return launch_tc<T, DD, CodeT, 1>(map, a, pl, stream);            \
+    case 2: return launch_tc<T, DD, CodeT, 2>(map, a, pl, stream);            \
+    case 4: return launch_tc<T, DD, CodeT, 4>(map, a, pl, stream);            \
+    default: return launch_tc<T, DD, CodeT, 0>(map, a, pl, stream);           \
   }
+  switch (d) {
+    case 4: PQ_TC_MT(4)
+    case 8: PQ_TC_MT(8)
+    default: PQ_TC_MT(16)
+  }
+#undef PQ_TC_MT
 }
 
 int gemm_tc_dispatch(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
@@ -470,7 +610,7 @@ int gemm_tc_dispatch(const void* x, int64_t x_stride, const void* codes, const v
   TcArgs a{};
   a.codes = codes; a.codebooks = codebooks; a.scales = scales; a.bias = bias; a.y = y; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
-  a.BN = pl.bn; a.n_tok_tiles = pl.n_tok_tiles; a.stages = pl.stages; a.cb_smem_bytes = pl.cb_smem;
+  a.BN = pl.bn; a.n_tok_tiles = pl.n_tok_tiles; a.stages = pl.stages; a.cb_smem_bytes = pl.cb_smem; a.cb_stride = pl.cb_stride;
   a.row_code_bytes = (int)(k / d * m * (nbits <= 8 ? 1 : 2));
   int rc = make_parts(a.parts, part_sizes, n_parts, n, kTcBM);
   if (rc) return rc;
