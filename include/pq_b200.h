@@ -62,7 +62,8 @@ enum {
   PQ_ALGO_AUTO = 0,
   PQ_ALGO_GEMV_DIRECT = 1, /* codebook gather in shared memory / L2, CUDA cores            */
   PQ_ALGO_GEMV_LUT = 2,    /* per-token x.centroid lookup tables (nbits <= 8)               */
-  PQ_ALGO_GEMM_TC = 3      /* dequant tile -> smem -> tcgen05.mma, TMEM accumulator         */
+  PQ_ALGO_GEMM_TC = 3,     /* dequant tile -> smem -> tcgen05.mma, TMEM accumulator         */
+  PQ_ALGO_GEMM_MMA = 4     /* codeword gather straight into mma.sync fragments (t <= 64)    */
 };
 
 PQ_API int pq_b200_abi_version(void);
@@ -76,6 +77,9 @@ PQ_API const char* pq_b200_strerror(int code);
  * max_active_clusters: cudaOccupancyMaxActiveClusters for the table GEMV. */
 PQ_API void pq_b200_debug_set_trace(void* device_buffer);
 PQ_API void pq_b200_debug_last_launch(int* out4);
+/* {token blocks, row tiles per step, cluster size, warps along K, superblocks per x phase,
+ * rows per cluster, grid.x, smem bytes} of the last PQ_ALGO_GEMM_MMA launch. */
+PQ_API void pq_b200_debug_last_mma_plan(int* out8);
 PQ_API int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes);
 
 /* Unscaled (scales == NULL; what aqlm_dequant returns, gemm_kernels.cu:563-592) or

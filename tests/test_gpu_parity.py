@@ -50,7 +50,8 @@ def test_golden_dequant_bit_exact(name):
 
 
 @pytest.mark.parametrize("name", G.names())
-@pytest.mark.parametrize("algo", [_lib.ALGO_AUTO, _lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_TC])
+@pytest.mark.parametrize("algo", [_lib.ALGO_AUTO, _lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_TC,
+                                  _lib.ALGO_GEMM_MMA])
 def test_golden_gemm(name, algo):
     c = dev(G.load(name))
     lib = _lib.load()
@@ -104,6 +105,27 @@ def test_gemm_sweep(fmt, dtype, t):
         assert torch.equal(yl, yl2)
 
 
+MMA_SWEEP = [(8, 8, 1), (8, 8, 2), (4, 8, 1), (6, 8, 2)]
+
+
+@pytest.mark.parametrize("fmt", MMA_SWEEP)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("t", [1, 2, 5, 8, 9, 16, 23, 32, 40, 64])
+@pytest.mark.parametrize("shape", [([128, 64, 72], 512), ([37], 8 * 48), ([1024, 48], 2048), ([200], 8 * 80)])
+def test_gemm_mma_sweep(fmt, dtype, t, shape):
+    """Register-fragment mma.sync kernel (2 <= T <= 64): ragged partitions, K that is not a
+    multiple of a 64-byte superblock, every token-block count, bias on even T."""
+    b, d, m = fmt
+    parts, k = shape
+    c = O.make_case(parts, k, b, d, m, t=t, dtype=dtype, seed=3 + t, bias=(t % 2 == 0))
+    g = dev(c)
+    assert _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMM_MMA, t, sum(parts), k, d, b, m)
+    y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMM_MMA)
+    check_output(y, c, "mma")
+    y2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMM_MMA)
+    assert torch.equal(y, y2)                    # fixed summation order
+
+
 TC_SWEEP = [(8, 8, 1), (8, 8, 2), (16, 8, 1), (4, 4, 1), (8, 16, 1), (12, 8, 1), (8, 8, 3), (12, 4, 2)]
 
 
@@ -121,9 +143,10 @@ def test_gemm_tc_sweep(fmt, dtype, t):
     y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMM_TC)
     check_output(y, c, "tc")
     # the A operand is the bit-exact dequantised weight and accumulation is fp32 in a fixed order:
-    # the result is reproducible, and equals what PQ_ALGO_AUTO picks for this token count
-    y2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"])
+    # the result is reproducible
+    y2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMM_TC)
     assert torch.equal(y, y2)
+    check_output(P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"]), c, "auto")
 
 
 def test_gemm_tc_prefill_full_size():
@@ -236,8 +259,8 @@ def test_full_size_properties(layer, fmt):
     ref = (g["x"].double() @ (w.double() * g["scales"].double().view(n, 1)).t())
     rms = float(((y.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()))
     assert rms < 2e-3, rms
-    for algo in (_lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT):
-        if algo == _lib.ALGO_GEMV_LUT and b > 8:
+    for algo in (_lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_MMA):
+        if algo != _lib.ALGO_GEMV_DIRECT and b > 8:
             continue
         ya = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, None, algo=algo)
         rms = float(((ya.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()))

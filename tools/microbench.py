@@ -1,6 +1,7 @@
 """Per-kernel timing on one GPU: rotates through enough distinct weight sets that codes do not
 stay L2-resident (>= 256 MB per timed loop), CUDA events on the launching stream."""
 import argparse
+import ctypes
 import json
 import os
 import sys
@@ -109,7 +110,7 @@ def main():
     P.ops.set_pdl(bool(a.pdl))
     global WARM_S
     WARM_S = a.warm
-    names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3}
+    names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3, "mma": 4}
     rows = []
     for sname in a.shapes.split(","):
         parts, k = SHAPES[sname]
@@ -135,7 +136,9 @@ def main():
                         print(f"skip {sname} {f} t={t} {an}: {exc}")
                         continue
                     ab = algo_bytes(t, n, k, d, b, m, len(parts))
-                    rows.append(dict(shape=sname, fmt=f, op="gemm", algo=an, t=t, us=dt * 1e6,
+                    plan = (ctypes.c_int * 8)()
+                    _lib.load().pq_b200_debug_last_mma_plan(plan)
+                    rows.append(dict(shape=sname, fmt=f, op="gemm", algo=an, t=t, us=dt * 1e6, mma_plan=list(plan),
                                      gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
                                      tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
                     print(rows[-1], flush=True)

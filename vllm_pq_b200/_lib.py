@@ -14,8 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpq_b200.so")
 
 PQ_F16, PQ_BF16 = 0, 1
-ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC = 0, 1, 2, 3
-ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc"}
+ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC, ALGO_GEMM_MMA = 0, 1, 2, 3, 4
+ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc", 4: "gemm_mma"}
 ABI_VERSION = 1
 MAX_PARTS = 8
 AR_FLAG_BYTES = 4096
@@ -30,6 +30,7 @@ SIGNATURES = {
     "pq_b200_strerror": (c_char_p, [c_int]),
     "pq_b200_debug_set_trace": (None, [c_void_p]),
     "pq_b200_debug_last_launch": (None, [ctypes.POINTER(c_int)]),
+    "pq_b200_debug_last_mma_plan": (None, [ctypes.POINTER(c_int)]),
     "pq_b200_debug_max_active_clusters": (c_int, [c_int, c_int]),
     "pq_b200_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
                                 c_int, c_int, _I64P, c_int, c_int, c_void_p]),

@@ -1,5 +1,7 @@
 // extern "C" surface of libpq_b200.so (see include/pq_b200.h).
 // Validates arguments, picks the kernel family, launches on the caller's stream.
+#include <cstdlib>
+
 #include "pq_common.cuh"
 
 namespace pq {
@@ -19,11 +21,16 @@ int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*
                      int, int, void*, int64_t, cudaStream_t);
 int64_t gemm_tc_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+int gemm_mma_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
+                      void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
+                      int, int, cudaStream_t);
+bool gemm_mma_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int allreduce_oneshot_dispatch(const void*, void*, int64_t, int, void* const*, void* const*, int, int,
                                int64_t, cudaStream_t);
 extern bool g_use_pdl;
 extern unsigned long long* g_lut_trace;
 extern int g_lut_last_grid[4];
+extern int g_mm_last_plan[8];
 int lut_max_active_clusters(int cs, int smem);
 }  // namespace pq
 
@@ -65,6 +72,7 @@ void pq_b200_set_pdl(int enabled) { pq::g_use_pdl = enabled != 0; }
 
 void pq_b200_debug_set_trace(void* device_buffer) { pq::g_lut_trace = (unsigned long long*)device_buffer; }
 void pq_b200_debug_last_launch(int* out4) { for (int i = 0; i < 4; ++i) out4[i] = pq::g_lut_last_grid[i]; }
+void pq_b200_debug_last_mma_plan(int* out8) { for (int i = 0; i < 8; ++i) out8[i] = pq::g_mm_last_plan[i]; }
 int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes) {
   return pq::lut_max_active_clusters(cluster_size, smem_bytes);
 }
@@ -81,8 +89,22 @@ int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales
 }
 
 int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  // Crossovers measured on B200 (profiles/r1_03_*): the register-fragment mma.sync kernel wins for
+  // 2..16 tokens everywhere and at 1 token / 32-64 tokens on the small-N layers (o_proj, down_proj),
+  // where the table GEMV's per-CTA table build and the tcgen05 kernel's per-tile dequant are not
+  // amortised.  Tuning knobs: PQ_T1_ALGO forces the batch-1 kernel, PQ_MMA_MAX_T caps the mma range.
+  static const int t1_algo = [] { const char* e = getenv("PQ_T1_ALGO"); return e ? atoi(e) : 0; }();
+  static const int mma_max_t = [] { const char* e = getenv("PQ_MMA_MAX_T"); return e ? atoi(e) : 64; }();
+  if (t == 1 && t1_algo && pq_b200_algo_supported(t1_algo, t, n, k, d, nbits, m)) return t1_algo;
+  const bool mma_ok = t <= mma_max_t && pq::gemm_mma_supported(t, n, k, d, nbits, m);
+  if (mma_ok) {
+    if (t >= 2 && t <= 16) return PQ_ALGO_GEMM_MMA;
+    if (t == 1 && n < 8192) return PQ_ALGO_GEMM_MMA;
+    if (t > 16 && n < 8192 && m == 1) return PQ_ALGO_GEMM_MMA;
+  }
   if (t > 8 && pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMM_TC;
   if (pq::gemv_lut_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
+  if (mma_ok) return PQ_ALGO_GEMM_MMA;
   return PQ_ALGO_GEMV_DIRECT;
 }
 
@@ -92,6 +114,7 @@ int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int
     case PQ_ALGO_AUTO: case PQ_ALGO_GEMV_DIRECT: return 1;
     case PQ_ALGO_GEMV_LUT: return pq::gemv_lut_supported(t, n, k, d, nbits, m) ? 1 : 0;
     case PQ_ALGO_GEMM_TC: return pq::gemm_tc_supported(t, n, k, d, nbits, m) ? 1 : 0;
+    case PQ_ALGO_GEMM_MMA: return pq::gemm_mma_supported(t, n, k, d, nbits, m) ? 1 : 0;
     default: return 0;
   }
 }
@@ -129,6 +152,10 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
       if (workspace_bytes < pq::gemm_tc_workspace(t, n, k, d, nbits, m, n_parts)) return PQ_ERR_WORKSPACE;
       return pq::gemm_tc_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
                                   nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+    case PQ_ALGO_GEMM_MMA:
+      if (!pq::gemm_mma_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+      return pq::gemm_mma_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
+                                   nbits, m, part_sizes, n_parts, dtype, s);
     default:
       return PQ_ERR_UNSUPPORTED;
   }
