@@ -33,7 +33,11 @@ def test_dequant_matches_reference_cuda(fmt, parts, k):
     if len(parts) == 1 or m == 1:
         assert torch.equal(ours.view(torch.int16), ref.view(torch.int16))
     else:
-        n0 = parts[0]
+        # ... except in the CTA that straddles the partition boundary: the reference stages ONE
+        # shared-memory codebook per CTA from per-warp pointers (gemm_kernels.cu:246-275), so the
+        # last <= 16 rows (thread_m, :350-358) of a partition whose size is not a multiple of the
+        # CTA's row count see a mix of both partitions' codebooks.  Compare below that.
+        n0 = parts[0] - 16
         assert torch.equal(ours[:n0].view(torch.int16), ref[:n0].view(torch.int16))
         oracle = O.dequantize_partitions(c["codes"].cpu(), c["codebooks"].cpu(), parts, None)
         assert torch.equal(ours.cpu().view(torch.int16), oracle.view(torch.int16))

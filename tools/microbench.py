@@ -105,6 +105,7 @@ def main():
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--warm", type=float, default=0.3)
     ap.add_argument("--nrep", type=int, default=0)
+    ap.add_argument("--ref", type=int, default=0, help="also time the reference's own CUDA kernels (oracle/_ref)")
     a = ap.parse_args()
     dtype = torch.float16 if a.dtype == "fp16" else torch.bfloat16
     P.ops.set_pdl(bool(a.pdl))
@@ -142,6 +143,17 @@ def main():
                                      gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
                                      tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
                     print(rows[-1], flush=True)
+                if a.ref:
+                    from oracle import ref_cuda as R
+                    if R.available() and R.supports(b, d, m, dtype):
+                        # what AQLMLinearMethod.apply runs: GEMV kernel up to 6 tokens, else dequant + F.linear
+                        fn = R.aqlm_gemm if t <= 6 else R.optimized_dequantize_gemm
+                        dt = time_loop(lambda s: fn(x, s[0], s[1], s[2], parts, None), sets, 5, graph=bool(a.graph))
+                        ab = algo_bytes(t, n, k, d, b, m, len(parts))
+                        rows.append(dict(shape=sname, fmt=f, op="gemm", algo="reference_cuda", t=t, us=dt * 1e6,
+                                         gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
+                                         tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
+                        print(rows[-1], flush=True)
             del sets
             torch.cuda.empty_cache()
     if a.out:
