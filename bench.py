@@ -217,8 +217,16 @@ def run_gpu_arm(args):
     y_host = torch.empty(B, shape.hidden, dtype=dtype).pin_memory()
     x_dev = x_host.to(device)
 
+    # torch's NCCL process group does not replay reliably from a captured CUDA graph (observed: hang at
+    # TP=2 with PQ_ONESHOT_ALLREDUCE=0); the one-shot NVLink kernel does.  Without it, TP > 1 runs eagerly.
+    use_graph = world == 1 or P.distributed.oneshot_enabled()
     with torch.no_grad():
-        graph, y_dev = capture(lambda: model(x_dev), stream)
+        if use_graph:
+            graph, y_dev = capture(lambda: model(x_dev), stream)
+        else:
+            graph = None
+            with torch.cuda.stream(stream):
+                y_dev = model(x_dev)
 
         # per-projection graphs: the same kernel over all layers' weights (cold L2), for the roofline
         kernel_rows = []
@@ -230,15 +238,21 @@ def run_gpu_arm(args):
                 g_k, _ = capture(lambda: [lin.quant_method.apply(lin, xin) for lin in lins], stream)
                 kernel_rows.append((name, lins[0], g_k, len(lins)))
 
+    def run_step():
+        if graph is not None:
+            graph.replay()
+            return y_dev
+        with torch.no_grad():
+            return model(x_dev)
+
     def step_resident():
         with torch.cuda.stream(stream):
-            graph.replay()
+            run_step()
 
     def step_e2e():
         with torch.cuda.stream(stream):
             x_dev.copy_(x_host, non_blocking=True)
-            graph.replay()
-            y_host.copy_(y_dev, non_blocking=True)
+            y_host.copy_(run_step(), non_blocking=True)
 
     def timed(run, steps):
         # events must be recorded on the launching stream
@@ -247,8 +261,9 @@ def run_gpu_arm(args):
 
     for _ in range(max(args.warmup, 3)):
         step_e2e()
-    t_warm = time.time() + 0.5                    # let clocks settle on a fresh box
-    while time.time() < t_warm:
+    # let clocks settle on a fresh box: a FIXED number of replays - a step contains collectives at
+    # TP > 1, so every rank must run exactly the same number of them (a time-based loop deadlocks)
+    for _ in range(300):
         step_resident()
     torch.cuda.synchronize()
 
@@ -277,7 +292,7 @@ def run_gpu_arm(args):
             "config": {"workload": f"{shape.name} all PQ linears ({len(model.layers)} layers x qkv,o,gate_up,down), decode",
                        "batch": B, "format": f"{b}bit x d{d} x M{m}", "parallelism": f"tp{world}",
                        "cold_l2": f"each step streams {model.code_bytes() * world / 1e6:.0f} MB of distinct codes (> 126 MB L2)",
-                       "launch": "CUDA graph" + (" + programmatic dependent launch" if args.pdl else ""),
+                       "launch": ("CUDA graph" if use_graph else "eager") + (" + programmatic dependent launch" if args.pdl else ""),
                        "allreduce": ("one-shot NVLink P2P kernel" if (world > 1 and P.distributed.oneshot_enabled())
                                      else ("nccl" if world > 1 else "none"))},
             "e2e": {"value": B / (ms_e2e * 1e-3), "unit": UNIT,
