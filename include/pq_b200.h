@@ -63,7 +63,8 @@ enum {
   PQ_ALGO_GEMV_DIRECT = 1, /* codebook gather in shared memory / L2, CUDA cores            */
   PQ_ALGO_GEMV_LUT = 2,    /* per-token x.centroid lookup tables (nbits <= 8)               */
   PQ_ALGO_GEMM_TC = 3,     /* dequant tile -> smem -> tcgen05.mma, TMEM accumulator         */
-  PQ_ALGO_GEMM_MMA = 4     /* codeword gather straight into mma.sync fragments (t <= 64)    */
+  PQ_ALGO_GEMM_MMA = 4,    /* codeword gather straight into mma.sync fragments (t <= 64)    */
+  PQ_ALGO_GEMV_LUT_TMA = 5 /* lookup tables, TMA code stream, one row per lane (nbits <= 8)  */
 };
 
 PQ_API int pq_b200_abi_version(void);

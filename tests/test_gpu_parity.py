@@ -51,7 +51,7 @@ def test_golden_dequant_bit_exact(name):
 
 @pytest.mark.parametrize("name", G.names())
 @pytest.mark.parametrize("algo", [_lib.ALGO_AUTO, _lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_TC,
-                                  _lib.ALGO_GEMM_MMA])
+                                  _lib.ALGO_GEMM_MMA, _lib.ALGO_GEMV_LUT_TMA])
 def test_golden_gemm(name, algo):
     c = dev(G.load(name))
     lib = _lib.load()
@@ -103,6 +103,37 @@ def test_gemm_sweep(fmt, dtype, t):
         # split-K partials are summed in a fixed order: the result is reproducible bit for bit
         yl2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT)
         assert torch.equal(yl, yl2)
+    if _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMV_LUT_TMA, t, n, k, d, b, m):
+        yt = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)
+        check_output(yt, c, "lut_tma")
+        yt2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)
+        assert torch.equal(yt, yt2)
+
+
+LUT_TMA_SWEEP = [(8, 8, 1), (8, 8, 2), (8, 8, 4), (4, 8, 1), (6, 8, 2), (8, 4, 1), (8, 16, 1), (5, 16, 2), (7, 4, 4)]
+
+
+@pytest.mark.parametrize("fmt", LUT_TMA_SWEEP)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("t", [1, 2, 5, 8])
+@pytest.mark.parametrize("shape", [([128, 64, 72], 64), ([65], 80), ([1024, 48], 256), ([200], 96), ([2500, 700], 144)])
+def test_gemm_lut_tma_sweep(fmt, dtype, t, shape):
+    """TMA-fed table GEMV (pq_gemv_lut2.cu): ragged partitions and row blocks that are not a
+    multiple of the 64-row box, K that ends inside a 64-position tile or a 16-byte chunk, every
+    cluster size the planner picks (1..8 tiles and more), several tiles per CTA, masked codes
+    (nbits < 8), 1..8 tokens on grid.y; reproducible bit for bit."""
+    b, d, m = fmt
+    parts, groups = shape
+    k = groups * d
+    n = sum(parts)
+    if not _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMV_LUT_TMA, t, n, k, d, b, m):
+        pytest.skip("code bytes per row not a multiple of 16")
+    c = O.make_case(parts, k, b, d, m, t=t, dtype=dtype, seed=7 + t, bias=(t % 2 == 0))
+    g = dev(c)
+    y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)
+    check_output(y, c, "lut_tma")
+    y2 = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)
+    assert torch.equal(y, y2)
 
 
 MMA_SWEEP = [(8, 8, 1), (8, 8, 2), (4, 8, 1), (6, 8, 2)]
@@ -259,7 +290,7 @@ def test_full_size_properties(layer, fmt):
     ref = (g["x"].double() @ (w.double() * g["scales"].double().view(n, 1)).t())
     rms = float(((y.double() - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()))
     assert rms < 2e-3, rms
-    for algo in (_lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_MMA):
+    for algo in (_lib.ALGO_GEMV_DIRECT, _lib.ALGO_GEMV_LUT, _lib.ALGO_GEMM_MMA, _lib.ALGO_GEMV_LUT_TMA):
         if algo != _lib.ALGO_GEMV_DIRECT and b > 8:
             continue
         ya = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, None, algo=algo)

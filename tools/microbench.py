@@ -111,7 +111,7 @@ def main():
     P.ops.set_pdl(bool(a.pdl))
     global WARM_S
     WARM_S = a.warm
-    names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3, "mma": 4}
+    names = {"auto": 0, "direct": 1, "lut": 2, "tc": 3, "mma": 4, "lut2": 5}
     rows = []
     for sname in a.shapes.split(","):
         parts, k = SHAPES[sname]

@@ -24,8 +24,11 @@ def main():
     ap.add_argument("--m", type=int, default=1)
     ap.add_argument("--t", type=int, default=1)
     ap.add_argument("--nsets", type=int, default=12)
+    ap.add_argument("--algo", type=int, default=_lib.ALGO_GEMV_LUT)
+    ap.add_argument("--pdl", type=int, default=0)
     a = ap.parse_args()
     lib = _lib.load()
+    P.ops.set_pdl(bool(a.pdl))
     for smem in (100 * 1024, 110 * 1024, 118 * 1024):
         print("max active clusters @%d KiB:" % (smem // 1024),
               {cs: lib.pq_b200_debug_max_active_clusters(cs, smem) for cs in (1, 2, 4, 8)})
@@ -39,10 +42,10 @@ def main():
     x = torch.randn(a.t, a.k, device="cuda", dtype=torch.float16)
     trace = torch.zeros(1 << 16, dtype=torch.int64, device="cuda")
     for s in sets:          # warm-up (also evicts the first sets from L2)
-        P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=_lib.ALGO_GEMV_LUT)
+        P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=a.algo)
     torch.cuda.synchronize()
     lib.pq_b200_debug_set_trace(trace.data_ptr())
-    P.ops.pq_gemm(x, sets[0][0], sets[0][1], sets[0][2], parts, None, algo=_lib.ALGO_GEMV_LUT)
+    P.ops.pq_gemm(x, sets[0][0], sets[0][1], sets[0][2], parts, None, algo=a.algo)
     torch.cuda.synchronize()
     lib.pq_b200_debug_set_trace(None)
     g = (ctypes.c_int * 4)()

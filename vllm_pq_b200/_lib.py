@@ -14,8 +14,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libpq_b200.so")
 
 PQ_F16, PQ_BF16 = 0, 1
-ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC, ALGO_GEMM_MMA = 0, 1, 2, 3, 4
-ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc", 4: "gemm_mma"}
+ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC, ALGO_GEMM_MMA, ALGO_GEMV_LUT_TMA = 0, 1, 2, 3, 4, 5
+ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc", 4: "gemm_mma", 5: "gemv_lut_tma"}
 ABI_VERSION = 1
 MAX_PARTS = 8
 AR_FLAG_BYTES = 4096

@@ -1,0 +1,660 @@
+// Decode-path PQ GEMV, lookup-table form, second generation (nbits <= 8): TMA-fed, one row per lane.
+//
+//   y[t, n] = scale[n] * sum_q LUT_t[q][code[n, q]] + bias[n]          q = g*M + m  ("position")
+//   LUT_t[q][e] = <codebook[p*M + q%M][e][:], x[t, (q/M)*d : (q/M+1)*d]>
+//
+// Semantics are aqlm.py:77-127 (dequantize + F.linear); there is no reference kernel of this shape.
+// What changed against pq_gemv_lut.cu (kept for T-pairs and as a cross-check):
+//  * codes arrive by TMA (cp.async.bulk.tensor.2d, boxes of 64 rows x 64 code bytes) issued by a
+//    producer warp, with a rolling cp.async.bulk.prefetch.tensor into L2 several row iterations
+//    ahead.  No LSU issue slots and no per-thread address arithmetic are spent on the stream, and
+//    under programmatic dependent launch the producer runs before griddepcontrol.wait: the next
+//    layer's codes are already in L2 / shared memory when its x arrives.
+//  * ONE LANE OWNS ONE ROW: no shuffles in the main loop, the per-row partial sum is a register.
+//  * the bank-conflict-free walk needs no register rotation: per code PRMT + LDS + FADD and nothing
+//    else (the old kernel spent ~2 more instructions per code on SEL/SHF/LOP rotations).
+//    Lane l (bits l4..l0) visits the 64 positions of its row in its own order; the order is built
+//    from three free things: the ADDRESS it loads its 16-byte code chunks from (chunk order and
+//    8-byte halves swapped by lane bits), the PRMT SELECTOR (a per-lane register: which byte of
+//    a code word goes first) and the TABLE COLUMN PERMUTATION below.
+//
+// Table layout: lut[e][col], 64 fp32 columns = 256 B per entry, so (code << 8 | column byte) is
+// ONE PRMT.  Position pos = 16 c + 4 j + b  (c: 16-byte chunk, j: word in chunk, b: byte in word)
+// lives in column  col = 32 (j & 1) + 16 (j >> 1) + 4 c + b,  bank = col % 32.
+// At step (v, j, b) of the walk lane l reads
+//      chunk c = (v + l[2:1]) & 3,  word j' = j ^ 2 l[3],  byte b' = (b + 2 l[4] + l[0]) & 3
+// so bank = 16 ((j>>1) ^ l[3]) + 4 ((v + l[2:1]) & 3) + ((b + 2 l[4] + l[0]) & 3): a bijection of
+// the 32 lanes onto the 32 banks at every step; the 128 (j & 1) part is an immediate offset.
+// The code words themselves are read with two LDS.64 per chunk from a dense [256 rows][64 B]
+// stage: address = row * 64 + 16 c + 8 (l[3] or !l[3]) - 16 distinct 8-byte bank pairs per
+// half-warp, conflict-free too.
+//
+// Split-K: a cluster of CS CTAs owns a block of rows; CTA `rank` owns position tiles rank, rank+CS..
+// Partial row sums are pushed through distributed shared memory and added in rank order
+// (deterministic); scale and bias are applied in fp32 before the single rounding of y.
+#include <cuda.h>
+
+#include <cstdlib>
+#include <type_traits>
+
+#include "pq_common.cuh"
+
+namespace pq {
+
+constexpr int kL2ConsWarps = 8;
+constexpr int kL2Cons = kL2ConsWarps * 32;          // consumer threads = rows per iteration
+constexpr int kL2Threads = kL2Cons + 32;            // + one producer warp
+constexpr int kL2Tile = 64;                         // positions per table = code bytes per row per box
+constexpr int kL2BoxRows = 64;
+constexpr int kL2BoxBytes = kL2BoxRows * kL2Tile;   // 4 KiB
+constexpr int kL2StageBytes = kL2Cons * kL2Tile;    // 16 KiB = 4 boxes
+constexpr int kL2MaxStages = 4;
+constexpr int kL2MaxCluster = 8;
+constexpr int kL2PrefetchAhead = 12;                // row iterations prefetched into L2 ahead of the loads
+constexpr int kL2MaxT = 8;
+
+struct Lut2Args {
+  const void* x; const void* codebooks; const void* scales; const void* bias; void* y;
+  long long x_stride, y_stride;
+  int T, N, K, E, M;
+  int Gp;                 // positions (= code bytes) per row
+  int n_tiles;            // ceil(Gp / 64)
+  int S;                  // tiles per CTA = ceil(n_tiles / CS)
+  int CS;                 // cluster size
+  int rows_per_cluster;   // multiple of 64
+  int stages;
+  int smem_cb, smem_x;    // bytes
+  int mask;               // nbits < 8: codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits)
+  unsigned long long* trace;
+  Parts parts;            // cta_end counts clusters
+};
+
+constexpr int kL2TraceSlots = 16;
+__device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
+  if (a.trace != nullptr && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
+  }
+}
+
+// ---- PTX wrappers ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t l2_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void l2_mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count));
+}
+__device__ __forceinline__ void l2_mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void l2_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void l2_mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}"
+      :: "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void l2_tma_load(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      :: "r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void l2_tma_prefetch(const CUtensorMap* map, int c0, int c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];"
+               :: "l"(map), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void l2_cp_async_16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void l2_cons_sync() {      // the 8 consumer warps only
+  asm volatile("bar.sync 1, %0;" :: "n"(kL2Cons) : "memory");
+}
+__device__ __forceinline__ uint32_t l2_cluster_rank() {
+  uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
+}
+__device__ __forceinline__ void l2_cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t l2_prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d; asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel)); return d;
+}
+template <int OFF> __device__ __forceinline__ float l2_lds(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+__device__ __forceinline__ void l2_lds64(uint32_t addr, uint32_t& a, uint32_t& b) {
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
+}
+
+template <typename T>
+__device__ __forceinline__ void l2_mma_k8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+  if constexpr (std::is_same<T, __half>::value)
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
+  else
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
+}
+template <typename T>
+__device__ __forceinline__ void l2_mma_k16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
+                                           uint32_t b0, uint32_t b1) {
+  if constexpr (std::is_same<T, __half>::value)
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  else
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// Half a table (the 32 positions with j & 1 == hb of one 64-position tile) on the tensor cores:
+// a tiny (E x D).(D x 32) GEMM.  cb: this partition's codebooks [M][E][D] in shared memory;
+// xt: the tile's x groups [64 / M][D] (zero beyond K) in shared memory.
+// MMA mapping (m16n8): rows = 16 entries; n-block jn (0..3) is byte b = jn of every word, so all
+// 8 columns of an n-block share codebook jn % M; its column cn is (chunk c = cn >> 1, word
+// j = hb + 2 (cn & 1)):  pos = 16 (cn >> 1) + 4 (hb + 2 (cn & 1)) + jn.
+// After the four n-blocks lane (g, tq) holds, for entries g and g + 8, the four bytes of word
+// (c = tq, j = hb) and of word (c = tq, j = hb + 2): columns 32 hb + 4 tq + {0..3} and
+// 32 hb + 16 + 4 tq + {0..3} - two 128-bit stores per entry row; odd g stores them in the other
+// order so that the 8 lanes of a store phase cover all 32 banks.
+template <typename T, int D, int M>
+__device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* xt, int E, int hb,
+                                              int warp, int lane) {
+  const int g = lane >> 2, tq = lane & 3;
+  constexpr int EW = D / 2;                        // u32 words per codebook entry / x group
+  const uint32_t* cb32 = reinterpret_cast<const uint32_t*>(cb);
+  const uint32_t* x32 = reinterpret_cast<const uint32_t*>(xt);
+
+  uint32_t b0[4], b1[4];
+#pragma unroll
+  for (int jn = 0; jn < 4; ++jn) {
+    const int pos = 16 * (g >> 1) + 4 * (hb + 2 * (g & 1)) + jn;   // B column n = g
+    const int grp = pos / M;
+    b0[jn] = 0u; b1[jn] = 0u;
+    if constexpr (D == 4) { if (tq < 2) b0[jn] = x32[grp * EW + tq]; }
+    else if constexpr (D == 8) { b0[jn] = x32[grp * EW + tq]; }
+    else { b0[jn] = x32[grp * EW + tq]; b1[jn] = x32[grp * EW + tq + 4]; }
+  }
+  for (int eb = warp; eb * 16 < E; eb += kL2ConsWarps) {
+    const int e0 = eb * 16 + g, e1 = e0 + 8;
+    uint32_t fa[M][4];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      const uint32_t* ca = cb32 + (m * E + e0) * EW;
+      const uint32_t* cbp = ca + 8 * EW;
+      const bool ok = (D != 4 || tq < 2);
+      fa[m][0] = ok ? ca[tq] : 0u;
+      fa[m][1] = ok ? cbp[tq] : 0u;
+      fa[m][2] = 0u; fa[m][3] = 0u;
+      if constexpr (D == 16) { fa[m][2] = ca[tq + 4]; fa[m][3] = cbp[tq + 4]; }
+    }
+    float a0[4], bb0[4], a1[4], bb1[4];            // word (tq, hb) / (tq, hb + 2) of entries e0 / e1
+#pragma unroll
+    for (int jn = 0; jn < 4; ++jn) {
+      const int m = jn % M;
+      float c[4] = {0.f, 0.f, 0.f, 0.f};
+      if constexpr (D == 16) l2_mma_k16<T>(c, fa[m][0], fa[m][1], fa[m][2], fa[m][3], b0[jn], b1[jn]);
+      else l2_mma_k8<T>(c, fa[m][0], fa[m][1], b0[jn]);
+      a0[jn] = c[0]; bb0[jn] = c[1]; a1[jn] = c[2]; bb1[jn] = c[3];
+    }
+    float4* r0 = reinterpret_cast<float4*>(lut + e0 * kL2Tile + 32 * hb + 4 * tq);
+    float4* r1 = reinterpret_cast<float4*>(lut + e1 * kL2Tile + 32 * hb + 4 * tq);
+    if (g & 1) {
+      r0[4] = make_float4(bb0[0], bb0[1], bb0[2], bb0[3]);
+      r0[0] = make_float4(a0[0], a0[1], a0[2], a0[3]);
+      r1[4] = make_float4(bb1[0], bb1[1], bb1[2], bb1[3]);
+      r1[0] = make_float4(a1[0], a1[1], a1[2], a1[3]);
+    } else {
+      r0[0] = make_float4(a0[0], a0[1], a0[2], a0[3]);
+      r0[4] = make_float4(bb0[0], bb0[1], bb0[2], bb0[3]);
+      r1[0] = make_float4(a1[0], a1[1], a1[2], a1[3]);
+      r1[4] = make_float4(bb1[0], bb1[1], bb1[2], bb1[3]);
+    }
+  }
+}
+
+template <typename T, int D>
+__device__ __forceinline__ void l2_build_table(float* lut, const T* cb, const T* xt, int E, int M,
+                                               int warp, int lane) {
+#pragma unroll
+  for (int hb = 0; hb < 2; ++hb) {
+    if (M == 1) l2_build_half<T, D, 1>(lut, cb, xt, E, hb, warp, lane);
+    else if (M == 2) l2_build_half<T, D, 2>(lut, cb, xt, E, hb, warp, lane);
+    else l2_build_half<T, D, 4>(lut, cb, xt, E, hb, warp, lane);
+  }
+}
+
+// 16 codes (one chunk) of one row: PRMT + LDS + FADD each.  cw[j] holds word j ^ 2 l[3] of the chunk,
+// colreg[jh] the four column bytes {0,4,8,12} + 16 c + 64 (jh ^ l[3]), sel[b] the lane's selectors.
+template <bool MASK>
+__device__ __forceinline__ void l2_lookup16(float& acc0, float& acc1, uint32_t lut_base, const uint32_t (&cw)[4],
+                                            const uint32_t (&colreg)[2], const uint32_t (&sel)[4], uint32_t emask4) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const uint32_t w = MASK ? (cw[j] & emask4) : cw[j];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const uint32_t off = l2_prmt(colreg[j >> 1], w, sel[b]);
+      const float v = (j & 1) ? l2_lds<128>(lut_base + off) : l2_lds<0>(lut_base + off);
+      if (b & 1) acc1 += v; else acc0 += v;
+    }
+  }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(kL2Threads, 2)
+pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
+  extern __shared__ __align__(1024) unsigned char l2_smem_raw[];
+  float* lut = reinterpret_cast<float*>(l2_smem_raw);
+  unsigned char* ring = l2_smem_raw + (size_t)a.E * (kL2Tile * 4);
+  T* cbs = reinterpret_cast<T*>(ring + (size_t)a.stages * kL2StageBytes);
+  T* xs = reinterpret_cast<T*>(reinterpret_cast<unsigned char*>(cbs) + a.smem_cb);
+  float* rowsum = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(xs) + a.smem_x);
+  float* recv = rowsum + a.rows_per_cluster;       // [CS][chunk] partial sums pushed by the peers
+  unsigned long long* bars = reinterpret_cast<unsigned long long*>(recv + a.rows_per_cluster + kL2MaxCluster);
+  const uint32_t full0 = l2_smem(bars), empty0 = full0 + 8 * kL2MaxStages;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int rank = a.CS > 1 ? (int)l2_cluster_rank() : 0;
+  const int tok = blockIdx.y;
+  l2_trace(a, 0);
+  const RowBlock rb = locate_row_block(a.parts, blockIdx.x / a.CS, a.rows_per_cluster);
+  const int rows = rb.row1 - rb.row0;
+  const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
+  // tiles of this CTA: rank, rank + CS, ... below n_tiles (CS <= n_tiles, so at least one)
+  const int my_tiles = (a.n_tiles - rank + a.CS - 1) / a.CS;
+
+  // the rows this CTA finishes: scale and bias are weights too - fetch them now (raw bits:
+  // converting here would stall on the load)
+  const int chunk = (rows + a.CS - 1) / a.CS;
+  const int fin0 = rank * chunk, fin1 = min(rows, fin0 + chunk);
+  unsigned short sc0_raw = 0, bi0_raw = 0;
+  if (fin0 + tid < fin1) {
+    sc0_raw = __ldg(reinterpret_cast<const unsigned short*>(a.scales) + rb.row0 + fin0 + tid);
+    if (a.bias) bi0_raw = __ldg(reinterpret_cast<const unsigned short*>(a.bias) + rb.row0 + fin0 + tid);
+  }
+
+  if (tid == 0) {
+    for (int i = 0; i < a.stages; ++i) {
+      l2_mbar_init(full0 + 8 * i, 1);
+      l2_mbar_init(empty0 + 8 * i, kL2ConsWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == kL2ConsWarps) {
+    // ================= producer warp: the whole code stream of this CTA, weights only ===========
+    pdl_launch_dependents();
+    if (lane == 0) {
+      const int total = my_tiles * n_iter;
+      const uint32_t ring_addr = l2_smem(ring);
+      auto boxes_of = [&](int it) { return min(4, (rows - it * kL2Cons + kL2BoxRows - 1) / kL2BoxRows); };
+      auto prefetch_item = [&](int i) {
+        const int s = i / n_iter, it = i - s * n_iter;
+        const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
+        const int nb = boxes_of(it);
+        for (int b = 0; b < nb; ++b) l2_tma_prefetch(&tmap, c0, r0 + b * kL2BoxRows);
+      };
+      const int pf0 = min(total, a.stages + kL2PrefetchAhead);
+      for (int i = a.stages; i < pf0; ++i) prefetch_item(i);
+      int stage = 0, round = 0;
+      for (int i = 0; i < total; ++i) {
+        const int s = i / n_iter, it = i - s * n_iter;
+        if (round > 0) l2_mbar_wait(empty0 + 8 * stage, (round - 1) & 1);
+        const int nb = boxes_of(it);
+        const uint32_t bar = full0 + 8 * stage;
+        l2_mbar_expect_tx(bar, nb * kL2BoxBytes);
+        const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
+        for (int b = 0; b < nb; ++b)
+          l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, c0, r0 + b * kL2BoxRows, bar);
+        if (i + a.stages + kL2PrefetchAhead < total) prefetch_item(i + a.stages + kL2PrefetchAhead);
+        if (++stage == a.stages) { stage = 0; ++round; }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ================= consumer warps ===========================================================
+    // weights that do not depend on the previous kernel: codebooks, scale and bias of the rows
+    // this CTA finishes
+    {
+      const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * a.smem_cb;
+      const uint32_t dst = l2_smem(cbs);
+      for (int i = tid; i < a.smem_cb / 16; i += kL2Cons) l2_cp_async_16(dst + i * 16, cb_g + (size_t)i * 16);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    l2_trace(a, 1);
+    pdl_launch_dependents();                       // the next layer may start fetching its weights
+    pdl_wait();                                    // x comes from the previous kernel
+    l2_trace(a, 2);
+
+    // ---- x of this CTA's tiles -> shared memory (zero beyond K) ----
+    {
+      const int gpt = kL2Tile / a.M;               // x groups per tile
+      const int wpt = gpt * D / 2;                 // u32 words per tile
+      uint32_t* xs32 = reinterpret_cast<uint32_t*>(xs);
+      const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
+      for (int s = 0; s < my_tiles; ++s) {
+        const int tile = s * a.CS + rank;
+        for (int w = tid; w < wpt; w += kL2Cons) {
+          const int elem = tile * gpt * D + 2 * w;
+          uint32_t v = 0u;
+          if (elem < a.K) v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
+          xs32[s * wpt + w] = v;
+        }
+      }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    l2_cons_sync();
+    l2_trace(a, 3);
+
+    // ---- lane constants of the conflict-free walk ----
+    const uint32_t lh = (lane >> 3) & 1, lc = (lane >> 1) & 3, lr = ((lane >> 4) << 1) | (lane & 1);
+    uint32_t sel[4];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const uint32_t bp = (b + lr) & 3;            // byte of the code word AND of colreg
+      sel[b] = ((8u | bp) << 12) | ((8u | bp) << 8) | ((4u + bp) << 4) | bp;   // {0, 0, code, column}
+    }
+    const uint32_t lut_base = l2_smem(lut);
+    const uint32_t emask4 = ((uint32_t)a.E - 1u) * 0x01010101u;
+    const uint32_t ring_addr = l2_smem(ring);
+    const uint32_t my_row_off = (uint32_t)tid * kL2Tile;
+
+    int stage = 0, round = 0;
+    for (int s = 0; s < my_tiles; ++s) {
+      if (s > 0) l2_cons_sync();                   // everyone is done with the previous table
+      l2_build_table<T, D>(lut, cbs, xs + (size_t)s * (kL2Tile / a.M) * D, a.E, a.M, warp, lane);
+      l2_cons_sync();
+      if (s == 0) l2_trace(a, 4);
+      for (int it = 0; it < n_iter; ++it) {
+        l2_mbar_wait(full0 + 8 * stage, round & 1);
+        const int row_l = it * kL2Cons + tid;
+        const bool active = row_l < rows;
+        uint32_t cw[4][4];
+        if (active) {
+          const uint32_t base = ring_addr + stage * kL2StageBytes + my_row_off;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const uint32_t ca = base + (((v + lc) & 3) << 4);
+            l2_lds64(ca + 8 * lh, cw[v][0], cw[v][1]);
+            l2_lds64(ca + 8 * (lh ^ 1), cw[v][2], cw[v][3]);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) l2_mbar_arrive(empty0 + 8 * stage);   // the stage may be refilled
+        if (++stage == a.stages) { stage = 0; ++round; }
+        if (active) {
+          float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            const uint32_t cbase = (16u * ((v + lc) & 3)) * 0x01010101u + 0x0C080400u;
+            uint32_t colreg[2];
+            colreg[0] = cbase + (64u * lh) * 0x01010101u;
+            colreg[1] = cbase + (64u * (lh ^ 1)) * 0x01010101u;
+            if (a.mask) l2_lookup16<true>(acc0, acc1, lut_base, cw[v], colreg, sel, emask4);
+            else l2_lookup16<false>(acc0, acc1, lut_base, cw[v], colreg, sel, emask4);   // uniform branch
+          }
+          const float r = acc0 + acc1;
+          if (s == 0) rowsum[row_l] = r; else rowsum[row_l] += r;
+        }
+      }
+    }
+    l2_trace(a, 5);
+  }
+  __syncthreads();
+
+  // ---- split-K over the cluster: every CTA pushes its partial sums of rows [o, o+1) * chunk into
+  // CTA o's receive buffer (distributed shared memory), ONE cluster barrier, then each CTA adds
+  // the CS partials of its own rows in rank order (deterministic), scales and stores ----
+  const float* fin = rowsum;                       // CS == 1: the sums are already final
+  int fin_parts = 1, part_stride = 0, fin_off = 0;
+  if (a.CS > 1) {
+    const uint32_t recv_addr = l2_smem(recv);
+    for (int i = tid; i < rows; i += kL2Threads) {
+      const int o = i / chunk, j = i - o * chunk;
+      uint32_t ra;
+      const uint32_t la = recv_addr + (uint32_t)(rank * chunk + j) * 4u;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(o));
+      asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(ra), "f"(rowsum[i]) : "memory");
+    }
+    l2_cluster_sync();
+    fin = recv; fin_parts = a.CS; part_stride = chunk; fin_off = -fin0;
+  }
+  l2_trace(a, 6);
+  for (int i = fin0 + tid; i < fin1; i += kL2Threads) {
+    const int row = rb.row0 + i;
+    float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
+    float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
+    if (i != fin0 + tid) {                         // chunk > blockDim: later rows fetch theirs here
+      sc = Traits<T>::to_f(reinterpret_cast<const T*>(a.scales)[row]);
+      b = a.bias ? Traits<T>::to_f(reinterpret_cast<const T*>(a.bias)[row]) : 0.f;
+    }
+    float sum = 0.f;
+    for (int r = 0; r < fin_parts; ++r) sum += fin[r * part_stride + i + fin_off];
+    reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+  }
+  l2_trace(a, 7);
+}
+
+// ------------------------------------------------------------------ host side
+extern bool g_use_pdl;
+extern unsigned long long* g_lut_trace;
+extern int g_lut_last_grid[4];
+
+struct Lut2Plan {
+  int cs, S, n_tiles, rows_per_cluster, stages, smem_cb, smem_x, smem_total;
+};
+
+static int lut2_smem_bytes(int E, int stages, int smem_cb, int smem_x, int rows) {
+  return E * kL2Tile * 4 + stages * kL2StageBytes + smem_cb + smem_x + (2 * rows + kL2MaxCluster) * 4 +
+         2 * 8 * kL2MaxStages;
+}
+
+constexpr int kL2TwoPerSm = 113 * 1024;            // two CTAs (this layer's + the next layer's) fit one SM
+
+// Co-resident clusters of `cs` CTAs at `smem` bytes per CTA (GPC granularity strands a few SMs
+// for cs >= 4).  Without a device: B200 figures.
+static int lut2_cluster_slots(int cs, int smem) {
+  static int cache[16][4][64] = {};                // device, log2(cs), smem / 4 KiB
+  int dev = 0;
+  const bool have_dev = cudaGetDevice(&dev) == cudaSuccess && dev < 16;
+  const int l2 = cs == 1 ? 0 : cs == 2 ? 1 : cs == 4 ? 2 : 3, sb = min(63, smem / 4096);
+  if (have_dev && cache[dev][l2][sb] > 0) return cache[dev][l2][sb];
+  int n = -1;
+  if (have_dev) {
+    auto kern = pq_gemv_lut2_kernel<__half, 8>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) == cudaSuccess) {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(kL2Threads); cfg.dynamicSmemBytes = (sb + 1) * 4096;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) n = -1;
+    }
+  }
+  if (n <= 0) {
+    cudaGetLastError();
+    static const int one[4] = {148, 74, 33, 15}, two[4] = {296, 148, 71, 33};
+    n = smem <= kL2TwoPerSm ? two[l2] : one[l2];
+  }
+  if (have_dev) cache[dev][l2][sb] = n;
+  return n;
+}
+
+static int64_t lut2_blocks(const int64_t* part_sizes, int n_parts, int64_t n, int rows) {
+  if (!part_sizes) return (n + rows - 1) / rows + (n_parts - 1);
+  int64_t b = 0;
+  for (int i = 0; i < n_parts; ++i) b += (part_sizes[i] + rows - 1) / rows;
+  return b;
+}
+
+// Cluster size and rows per cluster from a small cycle model: a CTA pays a fixed cost, one table
+// build per tile and 64 lookups per (tile, row); one CTA of this launch per SM where possible
+// (the second slot belongs to the next layer under programmatic dependent launch).
+static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                      const int64_t* part_sizes, int n_parts) {
+  const int E = 1 << nbits;
+  const int64_t gp = k / d * m;
+  pl.n_tiles = (int)((gp + kL2Tile - 1) / kL2Tile);
+  pl.smem_cb = m * E * d * 2;
+  static const int force_cs = [] { const char* e = getenv("PQ_LUT2_CS"); return e ? atoi(e) : 0; }();
+  static const int force_stages = [] { const char* e = getenv("PQ_LUT2_STAGES"); return e ? atoi(e) : 0; }();
+  static const int force_clusters = [] { const char* e = getenv("PQ_LUT2_CLUSTERS"); return e ? atoi(e) : 0; }();
+  const int sms = sm_count();
+  double best = 1e30;
+  bool found = false;
+  for (int cs = 1; cs <= kL2MaxCluster; cs *= 2) {
+    if (cs > pl.n_tiles) break;
+    if (force_cs && cs != force_cs) continue;
+    const int S = (pl.n_tiles + cs - 1) / cs;
+    const int smem_x = S * (kL2Tile / m) * d * 2;
+    if (smem_x > 32 * 1024) continue;
+    int slots1 = lut2_cluster_slots(cs, 200 * 1024);           // one CTA per SM
+    if (slots1 * cs > sms) slots1 = sms / cs;
+    int target = force_clusters ? force_clusters : slots1 / (int)t;
+    if (target < 1) target = 1;
+    int rows = (int)((n + target - 1) / target);
+    rows = (rows + kL2BoxRows - 1) / kL2BoxRows * kL2BoxRows;
+    const int max_rows = 4096;
+    if (rows > max_rows) rows = max_rows;
+    while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
+    const int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : 2;
+    const int smem = lut2_smem_bytes(E, stages, pl.smem_cb, smem_x, rows);
+    if (smem > 220 * 1024) continue;
+    const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, rows) * t;
+    const int slots = lut2_cluster_slots(cs, smem);
+    const int64_t waves = (blocks + slots - 1) / slots;
+    const double crowd = blocks > slots1 ? 1.6 : 1.0;          // two CTAs of this launch share an SM
+    const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
+    const double cta = 3000.0 + (cs > 1 ? 1200.0 : 0.0) +
+                       crowd * S * (700.0 * E / 256.0 + n_iter * 512.0 * 1.3);
+    const double cost = (double)waves * cta;
+    if (cost < best) {
+      best = cost; found = true;
+      pl.cs = cs; pl.S = S; pl.rows_per_cluster = rows; pl.stages = stages; pl.smem_x = smem_x;
+      pl.smem_total = smem;
+    }
+  }
+  return found;
+}
+
+bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  if (nbits > 8 || nbits < 4 || t > kL2MaxT || t < 1) return false;   // E >= 16: whole 16-entry MMA blocks
+  if (d != 4 && d != 8 && d != 16) return false;
+  if (m != 1 && m != 2 && m != 4) return false;
+  if (k % d) return false;
+  const int64_t gp = k / d * m;
+  if (gp % 16 || gp < kL2Tile || n < kL2BoxRows) return false;        // TMA: 16-byte row pitch, box inside the tensor
+  if (gp > (int64_t)1 << 30 || n > (int64_t)1 << 30) return false;
+  Lut2Plan pl;
+  return lut2_plan(pl, t, n, k, d, nbits, m, nullptr, PQ_MAX_PARTS);
+}
+
+// PQ_ALGO_AUTO heuristic: tiny problems are better served by the direct kernel.
+bool gemv_lut2_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  static const bool off = [] { const char* e = getenv("PQ_AUTO_LUT2"); return e && atoi(e) == 0; }();
+  return !off && gemv_lut2_supported(t, n, k, d, nbits, m) && n * (k / d * m) >= (1 << 18);
+}
+
+typedef CUresult (*PFN_l2TmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                          const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                          CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                          CUtensorMapFloatOOBfill);
+
+static PFN_l2TmapEncodeTiled lut2_tmap_encoder() {
+  static PFN_l2TmapEncodeTiled fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (PFN_l2TmapEncodeTiled)p;
+  }();
+  return fn;
+}
+
+// codes [N, Gp] bytes, row-major, as a 2-D tensor map: box = 64 code bytes x 64 rows, no swizzle,
+// out-of-bounds rows and positions read as zero.
+static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64_t gp) {
+  PFN_l2TmapEncodeTiled enc = lut2_tmap_encoder();
+  if (!enc) return PQ_ERR_UNSUPPORTED;
+  const cuuint64_t gdim[2] = {(cuuint64_t)gp, (cuuint64_t)n};
+  const cuuint64_t gstride[1] = {(cuuint64_t)gp};
+  const cuuint32_t box[2] = {(cuuint32_t)kL2Tile, (cuuint32_t)kL2BoxRows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(codes), gdim, gstride, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                         CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
+}
+
+template <typename T, int D>
+static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
+  auto kern = pq_gemv_lut2_kernel<T, D>;
+  static bool attr_set[64] = {};                   // per instantiation, per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!attr_set[dev & 63]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[dev & 63] = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.cs, a.T, 1);
+  cfg.blockDim = dim3(kL2Threads);
+  cfg.dynamicSmemBytes = pl.smem_total;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = pl.cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 2 : 1;
+  g_lut_last_grid[0] = cfg.gridDim.x; g_lut_last_grid[1] = cfg.gridDim.y;
+  g_lut_last_grid[2] = pl.cs; g_lut_last_grid[3] = pl.smem_total;
+  return (int)cudaLaunchKernelEx(&cfg, kern, map, a);
+}
+
+template <typename T>
+static int launch_lut2_d(const CUtensorMap& map, Lut2Args& a, int d, const Lut2Plan& pl, cudaStream_t stream) {
+  switch (d) {
+    case 4: return launch_lut2<T, 4>(map, a, pl, stream);
+    case 8: return launch_lut2<T, 8>(map, a, pl, stream);
+    default: return launch_lut2<T, 16>(map, a, pl, stream);
+  }
+}
+
+int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                       const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                       int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                       int n_parts, int dtype, cudaStream_t stream) {
+  if ((uintptr_t)codes % 16 || (uintptr_t)x % 4 || (x_stride * 2) % 4) return PQ_ERR_ALIGN;
+  Lut2Plan pl;
+  if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts)) return PQ_ERR_UNSUPPORTED;
+  Lut2Args a{};
+  a.x = x; a.codebooks = codebooks; a.scales = scales; a.bias = bias;
+  a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
+  a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
+  a.Gp = (int)(k / d * m); a.n_tiles = pl.n_tiles; a.S = pl.S; a.CS = pl.cs;
+  a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages;
+  a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
+  a.trace = g_lut_trace;
+  int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
+  if (rc) return rc;
+  CUtensorMap map;
+  rc = lut2_codes_tmap(&map, codes, n, a.Gp);
+  if (rc) return rc;
+  return dtype == PQ_F16 ? launch_lut2_d<__half>(map, a, d, pl, stream)
+                         : launch_lut2_d<__nv_bfloat16>(map, a, d, pl, stream);
+}
+
+}  // namespace pq
