@@ -9,7 +9,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import vllm_pq_b200 as P  # noqa: E402
 
-ALGOS = {"auto": 0, "direct": 1, "lut": 2, "tc": 3, "mma": 4}
+ALGOS = {"auto": 0, "direct": 1, "lut": 2, "tc": 3, "mma": 4, "lut2": 5}
 
 
 def main():

@@ -13,7 +13,9 @@ import vllm_pq_b200 as P  # noqa: E402
 from vllm_pq_b200 import _lib  # noqa: E402
 
 PHASES = ["start", "prefetch issued", "pdl wait done", "x staged + codebooks", "table 0 built",
-          "lookups done", "pushed + cluster barrier", "reduced + y stored"]
+          "lookups done", "pushed + cluster barrier", "reduced + y stored", "(lut_tma) barriers ready",
+          "(lut_tma) item 0 done", "(lut_tma) warp 0 table stores issued", "(lut_tma) x loads issued",
+          "(lut_tma) codebooks landed"]
 
 
 def main():

@@ -101,6 +101,8 @@ int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) 
   static const int t1_algo = [] { const char* e = getenv("PQ_T1_ALGO"); return e ? atoi(e) : 0; }();
   static const int mma_max_t = [] { const char* e = getenv("PQ_MMA_MAX_T"); return e ? atoi(e) : 64; }();
   if (t == 1 && t1_algo && pq_b200_algo_supported(t1_algo, t, n, k, d, nbits, m)) return t1_algo;
+  // one token: the TMA-fed table GEMV wins on every Llama projection (profiles/r1_13_microbench_lut2.jsonl)
+  if (t == 1 && pq::gemv_lut2_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT_TMA;
   const bool mma_ok = t <= mma_max_t && pq::gemm_mma_supported(t, n, k, d, nbits, m);
   if (mma_ok) {
     if (t >= 2 && t <= 16) return PQ_ALGO_GEMM_MMA;

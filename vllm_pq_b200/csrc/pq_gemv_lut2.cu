@@ -6,10 +6,10 @@
 // Semantics are aqlm.py:77-127 (dequantize + F.linear); there is no reference kernel of this shape.
 // What changed against pq_gemv_lut.cu (kept for T-pairs and as a cross-check):
 //  * codes arrive by TMA (cp.async.bulk.tensor.2d, boxes of 64 rows x 64 code bytes) issued by a
-//    producer warp, with a rolling cp.async.bulk.prefetch.tensor into L2 several row iterations
-//    ahead.  No LSU issue slots and no per-thread address arithmetic are spent on the stream, and
-//    under programmatic dependent launch the producer runs before griddepcontrol.wait: the next
-//    layer's codes are already in L2 / shared memory when its x arrives.
+//    producer warp into a 4-stage ring, with a rolling cp.async.bulk.prefetch.tensor into L2
+//    several row iterations ahead.  No LSU issue slots and no per-thread address arithmetic are
+//    spent on the stream, and the producer never waits for x: under programmatic dependent launch
+//    it runs ahead of griddepcontrol.wait.
 //  * ONE LANE OWNS ONE ROW: no shuffles in the main loop, the per-row partial sum is a register.
 //  * the bank-conflict-free walk needs no register rotation: per code PRMT + LDS + FADD and nothing
 //    else (the old kernel spent ~2 more instructions per code on SEL/SHF/LOP rotations).
@@ -41,16 +41,16 @@
 
 namespace pq {
 
-constexpr int kL2ConsWarps = 8;
+constexpr int kL2ConsWarps = 16;                    // four warps per scheduler: the lookups are latency-bound
 constexpr int kL2Cons = kL2ConsWarps * 32;          // consumer threads = rows per iteration
-constexpr int kL2Threads = kL2Cons + 32;            // + one producer warp
+constexpr int kL2Threads = kL2Cons + 32;            // + one producer warp (a TMA issue costs ~70 cycles)
 constexpr int kL2Tile = 64;                         // positions per table = code bytes per row per box
 constexpr int kL2BoxRows = 64;
 constexpr int kL2BoxBytes = kL2BoxRows * kL2Tile;   // 4 KiB
-constexpr int kL2StageBytes = kL2Cons * kL2Tile;    // 16 KiB = 4 boxes
+constexpr int kL2StageBoxes = kL2Cons / kL2BoxRows; // 8
+constexpr int kL2StageBytes = kL2Cons * kL2Tile;    // 32 KiB = 8 boxes
 constexpr int kL2MaxStages = 4;
 constexpr int kL2MaxCluster = 8;
-constexpr int kL2PrefetchAhead = 12;                // row iterations prefetched into L2 ahead of the loads
 constexpr int kL2MaxT = 8;
 
 struct Lut2Args {
@@ -63,6 +63,7 @@ struct Lut2Args {
   int CS;                 // cluster size
   int rows_per_cluster;   // multiple of 64
   int stages;
+  int prefetch;           // row iterations prefetched into L2 ahead of the ring
   int smem_cb, smem_x;    // bytes
   int mask;               // nbits < 8: codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits)
   unsigned long long* trace;
@@ -74,6 +75,17 @@ __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
   if (a.trace != nullptr && threadIdx.x == 0) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
+  }
+}
+
+// BAR.SYNC does not block at issue: a stamp right after a barrier shows when this warp ARRIVED.
+// This one waits for `dep` (a value read after the barrier from another warp's data) first.
+__device__ __forceinline__ void l2_trace_dep(const Lut2Args& a, int slot, const volatile uint32_t* p) {
+  if (a.trace != nullptr && threadIdx.x == 0) {
+    const uint32_t dep = *p;
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
     a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
   }
 }
@@ -133,15 +145,6 @@ __device__ __forceinline__ void l2_lds64(uint32_t addr, uint32_t& a, uint32_t& b
 }
 
 template <typename T>
-__device__ __forceinline__ void l2_mma_k8(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
-  if constexpr (std::is_same<T, __half>::value)
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
-  else
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(b0));
-}
-template <typename T>
 __device__ __forceinline__ void l2_mma_k16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3,
                                            uint32_t b0, uint32_t b1) {
   if constexpr (std::is_same<T, __half>::value)
@@ -154,9 +157,27 @@ __device__ __forceinline__ void l2_mma_k16(float (&c)[4], uint32_t a0, uint32_t 
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// x of one tile lives in shared memory in mma B-fragment order: word (hb, jn, lane) is what lane (g, tq)
+// feeds to n-block jn of half hb (column n = g: pos = 16 (g >> 1) + 4 (hb + 2 (g & 1)) + jn, k = 2 tq,
+// 2 tq + 1); D = 16 keeps the k + 8 words 256 further.  Conflict-free for every (D, M), and every
+// warp of the builder reads the same 8 words.
+template <int D> constexpr int l2_x_words() { return D == 16 ? 512 : 256; }
+// Element offset (inside the CTA's first tile, tile index `tile`) of fragment word f, or -1 for the
+// zero words of D = 4.  Computed before the dependency wait; after it each thread only adds the
+// tile step, loads 4 bytes and stores them.
+template <int D>
+__device__ __forceinline__ int l2_x_offset(int f, int tile, int M) {
+  const int gpt = kL2Tile / M;                     // x groups per tile
+  const int half = f >> 8, r = f & 255, hb = r >> 7, jn = (r >> 5) & 3, ln = r & 31;
+  const int g = ln >> 2, tq = ln & 3;
+  const int pos = 16 * (g >> 1) + 4 * (hb + 2 * (g & 1)) + jn;
+  if (D == 4 && tq >= 2) return -1;
+  return (tile * gpt + pos / M) * D + 2 * (tq + 4 * half);
+}
+
 // Half a table (the 32 positions with j & 1 == hb of one 64-position tile) on the tensor cores:
 // a tiny (E x D).(D x 32) GEMM.  cb: this partition's codebooks [M][E][D] in shared memory;
-// xt: the tile's x groups [64 / M][D] (zero beyond K) in shared memory.
+// xt: the tile's x in B-fragment order (l2_x_offset; zero beyond K) in shared memory.
 // MMA mapping (m16n8): rows = 16 entries; n-block jn (0..3) is byte b = jn of every word, so all
 // 8 columns of an n-block share codebook jn % M; its column cn is (chunk c = cn >> 1, word
 // j = hb + 2 (cn & 1)):  pos = 16 (cn >> 1) + 4 (hb + 2 (cn & 1)) + jn.
@@ -172,15 +193,12 @@ __device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* 
   const uint32_t* cb32 = reinterpret_cast<const uint32_t*>(cb);
   const uint32_t* x32 = reinterpret_cast<const uint32_t*>(xt);
 
+  // B fragments: staged in fragment order (l2_x_offset), the same for every warp and entry block
   uint32_t b0[4], b1[4];
 #pragma unroll
   for (int jn = 0; jn < 4; ++jn) {
-    const int pos = 16 * (g >> 1) + 4 * (hb + 2 * (g & 1)) + jn;   // B column n = g
-    const int grp = pos / M;
-    b0[jn] = 0u; b1[jn] = 0u;
-    if constexpr (D == 4) { if (tq < 2) b0[jn] = x32[grp * EW + tq]; }
-    else if constexpr (D == 8) { b0[jn] = x32[grp * EW + tq]; }
-    else { b0[jn] = x32[grp * EW + tq]; b1[jn] = x32[grp * EW + tq + 4]; }
+    b0[jn] = x32[(hb * 4 + jn) * 32 + lane];
+    b1[jn] = D == 16 ? x32[256 + (hb * 4 + jn) * 32 + lane] : 0u;
   }
   for (int eb = warp; eb * 16 < E; eb += kL2ConsWarps) {
     const int e0 = eb * 16 + g, e1 = e0 + 8;
@@ -201,7 +219,9 @@ __device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* 
       const int m = jn % M;
       float c[4] = {0.f, 0.f, 0.f, 0.f};
       if constexpr (D == 16) l2_mma_k16<T>(c, fa[m][0], fa[m][1], fa[m][2], fa[m][3], b0[jn], b1[jn]);
-      else l2_mma_k8<T>(c, fa[m][0], fa[m][1], b0[jn]);
+      // D <= 8: the k16 shape with a zero upper half - HMMA.16816 is the native shape on sm_100a,
+      // HMMA.1688 measured ~0.2 us slower per table (profiles/r1_12_trace_lut2.txt)
+      else l2_mma_k16<T>(c, fa[m][0], fa[m][1], 0u, 0u, b0[jn], 0u);
       a0[jn] = c[0]; bb0[jn] = c[1]; a1[jn] = c[2]; bb1[jn] = c[3];
     }
     float4* r0 = reinterpret_cast<float4*>(lut + e0 * kL2Tile + 32 * hb + 4 * tq);
@@ -233,8 +253,9 @@ __device__ __forceinline__ void l2_build_table(float* lut, const T* cb, const T*
 
 // 16 codes (one chunk) of one row: PRMT + LDS + FADD each.  cw[j] holds word j ^ 2 l[3] of the chunk,
 // colreg[jh] the four column bytes {0,4,8,12} + 16 c + 64 (jh ^ l[3]), sel[b] the lane's selectors.
+// Four independent add chains (one per byte step) keep the FADD latency off the critical path.
 template <bool MASK>
-__device__ __forceinline__ void l2_lookup16(float& acc0, float& acc1, uint32_t lut_base, const uint32_t (&cw)[4],
+__device__ __forceinline__ void l2_lookup16(float (&acc)[4], uint32_t lut_base, const uint32_t (&cw)[4],
                                             const uint32_t (&colreg)[2], const uint32_t (&sel)[4], uint32_t emask4) {
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -243,13 +264,14 @@ __device__ __forceinline__ void l2_lookup16(float& acc0, float& acc1, uint32_t l
     for (int b = 0; b < 4; ++b) {
       const uint32_t off = l2_prmt(colreg[j >> 1], w, sel[b]);
       const float v = (j & 1) ? l2_lds<128>(lut_base + off) : l2_lds<0>(lut_base + off);
-      if (b & 1) acc1 += v; else acc0 += v;
+      acc[b] += v;
     }
   }
 }
 
-template <typename T, int D>
-__global__ void __launch_bounds__(kL2Threads, 2)
+// MASK: nbits < 8 - codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits).
+template <typename T, int D, bool MASK>
+__global__ void __launch_bounds__(kL2Threads, 1)
 pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
   extern __shared__ __align__(1024) unsigned char l2_smem_raw[];
   float* lut = reinterpret_cast<float*>(l2_smem_raw);
@@ -262,14 +284,19 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   const uint32_t full0 = l2_smem(bars), empty0 = full0 + 8 * kL2MaxStages;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int rank = a.CS > 1 ? (int)l2_cluster_rank() : 0;
+  const bool clustered = a.CS > 1;
+  const int rank = clustered ? (int)l2_cluster_rank() : 0;
   const int tok = blockIdx.y;
   l2_trace(a, 0);
+  // every CTA of the cluster has started once this barrier phase completes (waited for just before
+  // the first distributed-shared-memory store, long after everyone arrived)
+  if (clustered) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   const RowBlock rb = locate_row_block(a.parts, blockIdx.x / a.CS, a.rows_per_cluster);
   const int rows = rb.row1 - rb.row0;
   const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
   // tiles of this CTA: rank, rank + CS, ... below n_tiles (CS <= n_tiles, so at least one)
   const int my_tiles = (a.n_tiles - rank + a.CS - 1) / a.CS;
+  const int total = my_tiles * n_iter;
 
   // the rows this CTA finishes: scale and bias are weights too - fetch them now (raw bits:
   // converting here would stall on the load)
@@ -281,6 +308,15 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     if (a.bias) bi0_raw = __ldg(reinterpret_cast<const unsigned short*>(a.bias) + rb.row0 + fin0 + tid);
   }
 
+  // this partition's codebooks: requested first of all, ahead of the bulk code stream in the
+  // memory queues (they gate the table build); consumer threads only - each waits for its own
+  if (tid < kL2Cons) {
+    const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * a.smem_cb;
+    const uint32_t dst = l2_smem(cbs);
+    for (int i = tid; i < a.smem_cb / 16; i += kL2Cons) l2_cp_async_16(dst + i * 16, cb_g + (size_t)i * 16);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  }
+
   if (tid == 0) {
     for (int i = 0; i < a.stages; ++i) {
       l2_mbar_init(full0 + 8 * i, 1);
@@ -289,22 +325,22 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  l2_trace(a, 8);
 
   if (warp == kL2ConsWarps) {
     // ================= producer warp: the whole code stream of this CTA, weights only ===========
     pdl_launch_dependents();
     if (lane == 0) {
-      const int total = my_tiles * n_iter;
       const uint32_t ring_addr = l2_smem(ring);
-      auto boxes_of = [&](int it) { return min(4, (rows - it * kL2Cons + kL2BoxRows - 1) / kL2BoxRows); };
+      auto boxes_of = [&](int it) {
+        return min(kL2StageBoxes, (rows - it * kL2Cons + kL2BoxRows - 1) / kL2BoxRows);
+      };
       auto prefetch_item = [&](int i) {
         const int s = i / n_iter, it = i - s * n_iter;
         const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         const int nb = boxes_of(it);
         for (int b = 0; b < nb; ++b) l2_tma_prefetch(&tmap, c0, r0 + b * kL2BoxRows);
       };
-      const int pf0 = min(total, a.stages + kL2PrefetchAhead);
-      for (int i = a.stages; i < pf0; ++i) prefetch_item(i);
       int stage = 0, round = 0;
       for (int i = 0; i < total; ++i) {
         const int s = i / n_iter, it = i - s * n_iter;
@@ -315,46 +351,17 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         for (int b = 0; b < nb; ++b)
           l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, c0, r0 + b * kL2BoxRows, bar);
-        if (i + a.stages + kL2PrefetchAhead < total) prefetch_item(i + a.stages + kL2PrefetchAhead);
+        // L2 prefetch runs a.prefetch items ahead of the ring (the ring itself holds `stages`)
+        if (i == 0)
+          for (int j = a.stages; j < min(total, a.stages + a.prefetch); ++j) prefetch_item(j);
+        else if (i + a.stages + a.prefetch - 1 < total) prefetch_item(i + a.stages + a.prefetch - 1);
         if (++stage == a.stages) { stage = 0; ++round; }
       }
     }
     __syncwarp();
+    if (clustered) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
   } else {
     // ================= consumer warps ===========================================================
-    // weights that do not depend on the previous kernel: codebooks, scale and bias of the rows
-    // this CTA finishes
-    {
-      const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * a.smem_cb;
-      const uint32_t dst = l2_smem(cbs);
-      for (int i = tid; i < a.smem_cb / 16; i += kL2Cons) l2_cp_async_16(dst + i * 16, cb_g + (size_t)i * 16);
-      asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-    l2_trace(a, 1);
-    pdl_launch_dependents();                       // the next layer may start fetching its weights
-    pdl_wait();                                    // x comes from the previous kernel
-    l2_trace(a, 2);
-
-    // ---- x of this CTA's tiles -> shared memory (zero beyond K) ----
-    {
-      const int gpt = kL2Tile / a.M;               // x groups per tile
-      const int wpt = gpt * D / 2;                 // u32 words per tile
-      uint32_t* xs32 = reinterpret_cast<uint32_t*>(xs);
-      const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
-      for (int s = 0; s < my_tiles; ++s) {
-        const int tile = s * a.CS + rank;
-        for (int w = tid; w < wpt; w += kL2Cons) {
-          const int elem = tile * gpt * D + 2 * w;
-          uint32_t v = 0u;
-          if (elem < a.K) v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
-          xs32[s * wpt + w] = v;
-        }
-      }
-    }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    l2_cons_sync();
-    l2_trace(a, 3);
-
     // ---- lane constants of the conflict-free walk ----
     const uint32_t lh = (lane >> 3) & 1, lc = (lane >> 1) & 3, lr = ((lane >> 4) << 1) | (lane & 1);
     uint32_t sel[4];
@@ -363,70 +370,120 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       const uint32_t bp = (b + lr) & 3;            // byte of the code word AND of colreg
       sel[b] = ((8u | bp) << 12) | ((8u | bp) << 8) | ((4u + bp) << 4) | bp;   // {0, 0, code, column}
     }
-    const uint32_t lut_base = l2_smem(lut);
-    const uint32_t emask4 = ((uint32_t)a.E - 1u) * 0x01010101u;
-    const uint32_t ring_addr = l2_smem(ring);
-    const uint32_t my_row_off = (uint32_t)tid * kL2Tile;
+    uint32_t colv[4][2];                           // column bytes of walk step v, word pair jh
+#pragma unroll
+    for (int v = 0; v < 4; ++v) {
+      const uint32_t cbase = (16u * ((v + lc) & 3)) * 0x01010101u + 0x0C080400u;
+      colv[v][0] = cbase + (64u * lh) * 0x01010101u;
+      colv[v][1] = cbase + (64u * (lh ^ 1)) * 0x01010101u;
+    }
+    uint32_t lut_base = l2_smem(lut);
+    uint32_t emask4 = ((uint32_t)a.E - 1u) * 0x01010101u;
+    uint32_t recv_addr = l2_smem(recv);
+    uint32_t caddr[4];                             // first 8-byte half of walk step v in stage 0
+#pragma unroll
+    for (int v = 0; v < 4; ++v)
+      caddr[v] = l2_smem(ring) + (uint32_t)tid * kL2Tile + (((v + lc) & 3) << 4) + 8 * lh;
+    // x: this thread's word of the B-fragment layout
+    constexpr int XW = l2_x_words<D>();
+    int xoff = tid < XW ? l2_x_offset<D>(tid, rank, a.M) : -1;
+    int xstep = a.CS * (kL2Tile / a.M) * D;        // elements between this CTA's consecutive tiles
+    const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
+    uint32_t* xs_mine = reinterpret_cast<uint32_t*>(xs) + tid;
+    // all of the above is integer work on lane ids and launch constants: make sure it is done
+    // BEFORE the dependency wait (16 warps share 4 schedulers - every instruction after the wait
+    // is on the layer's critical path four times over)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      asm volatile("" : "+r"(sel[i]), "+r"(colv[i][0]), "+r"(colv[i][1]), "+r"(caddr[i]));
+    }
+    asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xoff), "+r"(xstep), "+l"(xg), "+l"(xs_mine));
 
+    // codes of one item (row iteration `it` of a tile) -> registers; the stage is released at once
     int stage = 0, round = 0;
+    auto load_codes = [&](uint32_t (&cw)[4][4], int it) {
+      l2_mbar_wait(full0 + 8 * stage, round & 1);
+      if (it * kL2Cons + tid < rows) {
+        const uint32_t so = stage * kL2StageBytes;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          l2_lds64(caddr[v] + so, cw[v][0], cw[v][1]);
+          l2_lds64((caddr[v] ^ 8u) + so, cw[v][2], cw[v][3]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) l2_mbar_arrive(empty0 + 8 * stage);
+      if (++stage == a.stages) { stage = 0; ++round; }
+    };
+    // 64 lookups of one row; on the CTA's last tile the row's partial sum goes straight to the
+    // CTA that finishes the row (distributed shared memory), else it is kept in rowsum
+    auto lookups = [&](const uint32_t (&cw)[4][4], int s, int it) {
+      const int row_l = it * kL2Cons + tid;
+      if (row_l < rows) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int v = 0; v < 4; ++v) l2_lookup16<MASK>(acc, lut_base, cw[v], colv[v], sel, emask4);
+        float r = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+        if (s > 0) r += rowsum[row_l];
+        if (s + 1 < my_tiles || !clustered) {
+          rowsum[row_l] = r;
+        } else {
+          const int o = row_l / chunk, j = row_l - o * chunk;
+          uint32_t ra;
+          const uint32_t la = recv_addr + (uint32_t)(rank * chunk + j) * 4u;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(o));
+          asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(ra), "f"(r) : "memory");
+        }
+      }
+    };
+
+    l2_trace(a, 1);
+    pdl_launch_dependents();                       // the next layer may start fetching its weights
+    pdl_wait();                                    // x comes from the previous kernel
+    l2_trace(a, 2);
+
+    // ---- x of this CTA's tiles -> shared memory, B-fragment order (zero beyond K) ----
+    if (tid < XW) {
+      for (int s = 0; s < my_tiles; ++s) {
+        const int elem = xoff + s * xstep;
+        uint32_t v = 0u;
+        if (xoff >= 0 && elem < a.K) v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
+        xs_mine[s * XW] = v;
+      }
+    }
+    l2_trace(a, 11);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    l2_trace(a, 12);
+    l2_cons_sync();
+    l2_trace_dep(a, 3, reinterpret_cast<const volatile uint32_t*>(xs) + 255);
+
     for (int s = 0; s < my_tiles; ++s) {
       if (s > 0) l2_cons_sync();                   // everyone is done with the previous table
-      l2_build_table<T, D>(lut, cbs, xs + (size_t)s * (kL2Tile / a.M) * D, a.E, a.M, warp, lane);
+      l2_build_table<T, D>(lut, cbs, xs + (size_t)s * l2_x_words<D>() * 2, a.E, a.M, warp, lane);
+      if (s == 0) l2_trace(a, 10);
       l2_cons_sync();
-      if (s == 0) l2_trace(a, 4);
+      if (s == 0) l2_trace_dep(a, 4, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
+      if (s + 1 == my_tiles && clustered) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
       for (int it = 0; it < n_iter; ++it) {
-        l2_mbar_wait(full0 + 8 * stage, round & 1);
-        const int row_l = it * kL2Cons + tid;
-        const bool active = row_l < rows;
         uint32_t cw[4][4];
-        if (active) {
-          const uint32_t base = ring_addr + stage * kL2StageBytes + my_row_off;
-#pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            const uint32_t ca = base + (((v + lc) & 3) << 4);
-            l2_lds64(ca + 8 * lh, cw[v][0], cw[v][1]);
-            l2_lds64(ca + 8 * (lh ^ 1), cw[v][2], cw[v][3]);
-          }
-        }
-        __syncwarp();
-        if (lane == 0) l2_mbar_arrive(empty0 + 8 * stage);   // the stage may be refilled
-        if (++stage == a.stages) { stage = 0; ++round; }
-        if (active) {
-          float acc0 = 0.f, acc1 = 0.f;
-#pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            const uint32_t cbase = (16u * ((v + lc) & 3)) * 0x01010101u + 0x0C080400u;
-            uint32_t colreg[2];
-            colreg[0] = cbase + (64u * lh) * 0x01010101u;
-            colreg[1] = cbase + (64u * (lh ^ 1)) * 0x01010101u;
-            if (a.mask) l2_lookup16<true>(acc0, acc1, lut_base, cw[v], colreg, sel, emask4);
-            else l2_lookup16<false>(acc0, acc1, lut_base, cw[v], colreg, sel, emask4);   // uniform branch
-          }
-          const float r = acc0 + acc1;
-          if (s == 0) rowsum[row_l] = r; else rowsum[row_l] += r;
-        }
+        load_codes(cw, it);
+        lookups(cw, s, it);
+        if (s == 0 && it == 0) l2_trace(a, 9);
       }
     }
     l2_trace(a, 5);
   }
-  __syncthreads();
 
-  // ---- split-K over the cluster: every CTA pushes its partial sums of rows [o, o+1) * chunk into
-  // CTA o's receive buffer (distributed shared memory), ONE cluster barrier, then each CTA adds
-  // the CS partials of its own rows in rank order (deterministic), scales and stores ----
+  // ---- split-K over the cluster: the partial sums of rows [o, o+1) * chunk were pushed into CTA
+  // o's receive buffer; ONE cluster barrier, then each CTA adds the CS partials of its own rows in
+  // rank order (deterministic), scales and stores ----
   const float* fin = rowsum;                       // CS == 1: the sums are already final
   int fin_parts = 1, part_stride = 0, fin_off = 0;
-  if (a.CS > 1) {
-    const uint32_t recv_addr = l2_smem(recv);
-    for (int i = tid; i < rows; i += kL2Threads) {
-      const int o = i / chunk, j = i - o * chunk;
-      uint32_t ra;
-      const uint32_t la = recv_addr + (uint32_t)(rank * chunk + j) * 4u;
-      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(o));
-      asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(ra), "f"(rowsum[i]) : "memory");
-    }
+  if (clustered) {
     l2_cluster_sync();
     fin = recv; fin_parts = a.CS; part_stride = chunk; fin_off = -fin0;
+  } else {
+    __syncthreads();
   }
   l2_trace(a, 6);
   for (int i = fin0 + tid; i < fin1; i += kL2Threads) {
@@ -470,7 +527,7 @@ static int lut2_cluster_slots(int cs, int smem) {
   if (have_dev && cache[dev][l2][sb] > 0) return cache[dev][l2][sb];
   int n = -1;
   if (have_dev) {
-    auto kern = pq_gemv_lut2_kernel<__half, 8>;
+    auto kern = pq_gemv_lut2_kernel<__half, 8, false>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) == cudaSuccess) {
       cudaLaunchConfig_t cfg{};
       cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(kL2Threads); cfg.dynamicSmemBytes = (sb + 1) * 4096;
@@ -516,7 +573,7 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
     if (cs > pl.n_tiles) break;
     if (force_cs && cs != force_cs) continue;
     const int S = (pl.n_tiles + cs - 1) / cs;
-    const int smem_x = S * (kL2Tile / m) * d * 2;
+    const int smem_x = S * (d == 16 ? 512 : 256) * 4;      // B-fragment order, see l2_stage_x
     if (smem_x > 32 * 1024) continue;
     int slots1 = lut2_cluster_slots(cs, 200 * 1024);           // one CTA per SM
     if (slots1 * cs > sms) slots1 = sms / cs;
@@ -527,16 +584,18 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
     const int max_rows = 4096;
     if (rows > max_rows) rows = max_rows;
     while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
-    const int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : 2;
-    const int smem = lut2_smem_bytes(E, stages, pl.smem_cb, smem_x, rows);
+    const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
+    int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(kL2MaxStages, max(2, S * n_iter));
+    auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, pl.smem_cb, smem_x, rows); };
+    while (stages > 2 && smem_of(stages) > 220 * 1024) --stages;
+    const int smem = smem_of(stages);
     if (smem > 220 * 1024) continue;
     const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, rows) * t;
     const int slots = lut2_cluster_slots(cs, smem);
     const int64_t waves = (blocks + slots - 1) / slots;
     const double crowd = blocks > slots1 ? 1.6 : 1.0;          // two CTAs of this launch share an SM
-    const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
     const double cta = 3000.0 + (cs > 1 ? 1200.0 : 0.0) +
-                       crowd * S * (700.0 * E / 256.0 + n_iter * 512.0 * 1.3);
+                       crowd * S * (700.0 * E / 256.0 + n_iter * 1024.0 * 1.3);
     const double cost = (double)waves * cta;
     if (cost < best) {
       best = cost; found = true;
@@ -597,9 +656,9 @@ static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-template <typename T, int D>
+template <typename T, int D, bool MASK>
 static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  auto kern = pq_gemv_lut2_kernel<T, D>;
+  auto kern = pq_gemv_lut2_kernel<T, D, MASK>;
   static bool attr_set[64] = {};                   // per instantiation, per device
   int dev = 0;
   cudaGetDevice(&dev);
@@ -626,10 +685,17 @@ static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, 
 
 template <typename T>
 static int launch_lut2_d(const CUtensorMap& map, Lut2Args& a, int d, const Lut2Plan& pl, cudaStream_t stream) {
+  if (a.mask) {
+    switch (d) {
+      case 4: return launch_lut2<T, 4, true>(map, a, pl, stream);
+      case 8: return launch_lut2<T, 8, true>(map, a, pl, stream);
+      default: return launch_lut2<T, 16, true>(map, a, pl, stream);
+    }
+  }
   switch (d) {
-    case 4: return launch_lut2<T, 4>(map, a, pl, stream);
-    case 8: return launch_lut2<T, 8>(map, a, pl, stream);
-    default: return launch_lut2<T, 16>(map, a, pl, stream);
+    case 4: return launch_lut2<T, 4, false>(map, a, pl, stream);
+    case 8: return launch_lut2<T, 8, false>(map, a, pl, stream);
+    default: return launch_lut2<T, 16, false>(map, a, pl, stream);
   }
 }
 
@@ -646,6 +712,9 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
   a.Gp = (int)(k / d * m); a.n_tiles = pl.n_tiles; a.S = pl.S; a.CS = pl.cs;
   a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages;
+  static const int prefetch = [] { const char* e = getenv("PQ_LUT2_PREFETCH"); return e ? atoi(e) : 8; }();
+  a.prefetch = prefetch;
+
   a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
   a.trace = g_lut_trace;
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
