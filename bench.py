@@ -46,6 +46,16 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_traffic(model: str, fmt: str, dtype: str, world: int, batch: int, kernel: str):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.isfile(path):
+        return None
+    with open(path) as fh:
+        table = json.load(fh)
+    return table.get(f"{model}/{fmt}/{dtype}/tp{world}/batch{batch}", {}).get(kernel)
+
+
 def parse_format(s: str):
     b, d, m = (int(v) for v in s.split("x"))
     return b, d, m
@@ -301,7 +311,9 @@ def run_gpu_arm(args):
             "gpu_launches": model.launches_per_step() * args.steps,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
-                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / hbm_gbs,
+                         "traffic": measured_traffic(args.model, args.format, args.dtype, world, B, dom),
+                         "algorithmic_bytes": kernels[dom]["algorithmic_bytes"], "peak_source": peak_src,
                          "whole_step_gbs": sum(v["algorithmic_bytes"] for v in kernels.values()) * len(model.layers)
                          / (ms_step * 1e-3) / 1e9},
             "kernels": kernels,

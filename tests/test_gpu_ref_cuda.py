@@ -59,11 +59,24 @@ def test_gemv_matches_reference_cuda(fmt, t, parts, k, bias):
     ref = R.aqlm_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"])
     torch.cuda.synchronize()
     exact = O.linear_fp32(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"])
-    e_ours, e_ref = O.error_report(ours.cpu(), exact), O.error_report(ref.cpu(), exact)
+    e_ours = O.error_report(ours.cpu(), exact)
     assert e_ours["rms_rel"] <= 2e-3, e_ours
+    # Code2x8MatVec stages ONE shared-memory codebook per CTA from per-warp pointers
+    # (gemm_kernels.cu:114-141) and its rows per CTA follow the SM count (:331-338, <= 16): on a
+    # 148-SM part CTAs straddle the partition boundaries and up to 16 rows either side of one see
+    # the wrong partition's codebooks.  Those rows are left out of the comparison WITH THE
+    # REFERENCE KERNEL only (ours is checked on every row above).
+    keep = torch.ones(sum(parts), dtype=torch.bool)
+    if m > 1 and len(parts) > 1:
+        edge = 0
+        for p_rows in parts[:-1]:
+            edge += p_rows
+            keep[max(0, edge - 16):edge + 16] = False
+    e_ours_k = O.error_report(ours.cpu()[:, keep], exact[:, keep])
+    e_ref = O.error_report(ref.cpu()[:, keep], exact[:, keep])
     assert e_ref["rms_rel"] <= 4e-3, e_ref
-    assert e_ours["rms_rel"] <= e_ref["rms_rel"] * 1.5 + 1e-6, (e_ours, e_ref)
-    torch.testing.assert_close(ours.float(), ref.float(), rtol=2e-2,
+    assert e_ours_k["rms_rel"] <= e_ref["rms_rel"] * 1.5 + 1e-6, (e_ours_k, e_ref)
+    torch.testing.assert_close(ours.float()[:, keep.cuda()], ref.float()[:, keep.cuda()], rtol=2e-2,
                                atol=2e-2 * float(exact.abs().max()))
 
 
