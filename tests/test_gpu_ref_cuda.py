@@ -72,6 +72,9 @@ def test_gemv_matches_reference_cuda(fmt, t, parts, k, bias):
         for p_rows in parts[:-1]:
             edge += p_rows
             keep[max(0, edge - 16):edge + 16] = False
+        # ... and the last CTA: its warps beyond the last row never advance their codebook pointer
+        # (gemm_kernels.cu:117-126) but still take part in the staging loop
+        keep[-16:] = False
     e_ours_k = O.error_report(ours.cpu()[:, keep], exact[:, keep])
     e_ref = O.error_report(ref.cpu()[:, keep], exact[:, keep])
     assert e_ref["rms_rel"] <= 4e-3, e_ref

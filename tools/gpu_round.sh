@@ -1,11 +1,12 @@
 set -x
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_ref_cuda.py -x -q -k "test_gemv_matches_reference_cuda" 2>&1 | tail -4
-PQ_AUTO_LUT2=0 timeout 300 python -m pytest tests/test_gpu_ref_cuda.py -x -q -k "test_gemv_matches_reference_cuda" 2>&1 | tail -4
-timeout 300 python -m pytest "tests/test_gpu_ref_cuda.py::test_gemv_matches_reference_cuda[False-parts1-2048-1-fmt1]" -x -q 2>&1 | tail -4
-timeout 600 compute-sanitizer --tool memcheck python tools/run_one.py --parts 1024,512,512 --k 2048 --fmt 8x8x2 --algo lut2 --nsets 2 --iters 2 > gpurun_out/r1_17_sanitizer.log 2>&1; echo "sanitizer rc=$?"
-tail -15 gpurun_out/r1_17_sanitizer.log
-for cs in 4 8; do
-  echo "== CS=$cs"
-  PQ_LUT2_CS=$cs timeout 300 python tools/microbench.py --shapes qkv7b,o7b,gateup7b,down7b --formats 8x8x1 --tokens 1 --algos lut2 --pdl 1 --dequant 0 2>&1 | grep -o "'shape': '[a-z0-9]*'.*'us': [0-9.]*"
-done
+timeout 900 python -m pytest tests/test_gpu_ref_cuda.py -x -q 2>&1 | tail -3
+timeout 600 python tools/microbench.py --shapes qkv7b,o7b,gateup7b,down7b,gateup70b,down70b --formats 8x8x1,8x8x2 --tokens 1 --algos lut2 --pdl 1 --dequant 0 > gpurun_out/r1_19_microbench_lut2.jsonl 2>&1; echo "microbench rc=$?"
+python - <<'PY'
+import ast
+for l in open('gpurun_out/r1_19_microbench_lut2.jsonl'):
+    l=l.strip()
+    if l.startswith('{'):
+        d=ast.literal_eval(l); print(d['shape'],d['fmt'],d['algo'],'us=%.1f gbs=%.0f'%(d['us'],d['gbs']))
+    else: print(l)
+PY

@@ -18,7 +18,8 @@ bool gemv_lut_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m
 bool gemv_lut_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemv_lut2_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
                        void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
-                       int, int, cudaStream_t);
+                       int, int, void*, int64_t, cudaStream_t);
+int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 bool gemv_lut2_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
@@ -132,6 +133,7 @@ int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d
   if (algo == PQ_ALGO_AUTO) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
   if (algo == PQ_ALGO_GEMV_LUT) return pq::gemv_lut_workspace(t, n, k, d, nbits, m, n_parts);
   if (algo == PQ_ALGO_GEMM_TC) return pq::gemm_tc_workspace(t, n, k, d, nbits, m, n_parts);
+  if (algo == PQ_ALGO_GEMV_LUT_TMA) return pq::gemv_lut2_workspace(t, n, k, d, nbits, m, n_parts);
   return 0;
 }
 
@@ -163,7 +165,7 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
     case PQ_ALGO_GEMV_LUT_TMA:
       if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
-                                    nbits, m, part_sizes, n_parts, dtype, s);
+                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
     case PQ_ALGO_GEMM_MMA:
       if (!pq::gemm_mma_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemm_mma_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,

@@ -62,6 +62,9 @@ struct Lut2Args {
   int S;                  // tiles per CTA = ceil(n_tiles / CS)
   int CS;                 // cluster size
   int rows_per_cluster;   // multiple of 64
+  int KG;                 // clusters along K per row block (each owns CS * S consecutive tiles)
+  float* ws_part;         // KG > 1: [T][KG][N] fp32 partial sums (workspace)
+  int* ws_tickets;        // KG > 1: one counter per (token, row block, rank); zero between launches
   int stages;
   int prefetch;           // row iterations prefetched into L2 ahead of the ring
   int smem_cb, smem_x;    // bytes
@@ -291,11 +294,14 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   // every CTA of the cluster has started once this barrier phase completes (waited for just before
   // the first distributed-shared-memory store, long after everyone arrived)
   if (clustered) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
-  const RowBlock rb = locate_row_block(a.parts, blockIdx.x / a.CS, a.rows_per_cluster);
+  const int cid = blockIdx.x / a.CS;               // cluster: (row block, K group)
+  const int block = cid / a.KG, kg = cid - block * a.KG;
+  const int tile0 = kg * a.CS * a.S + rank;        // this CTA's tiles: tile0, tile0 + CS, ... (S of them)
+  const RowBlock rb = locate_row_block(a.parts, block, a.rows_per_cluster);
   const int rows = rb.row1 - rb.row0;
   const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
-  // tiles of this CTA: rank, rank + CS, ... below n_tiles (CS <= n_tiles, so at least one)
-  const int my_tiles = (a.n_tiles - rank + a.CS - 1) / a.CS;
+  // tiles of this CTA that exist (the last K group may leave some ranks with none)
+  const int my_tiles = tile0 < a.n_tiles ? min(a.S, (a.n_tiles - tile0 + a.CS - 1) / a.CS) : 0;
   const int total = my_tiles * n_iter;
 
   // the rows this CTA finishes: scale and bias are weights too - fetch them now (raw bits:
@@ -337,7 +343,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       };
       auto prefetch_item = [&](int i) {
         const int s = i / n_iter, it = i - s * n_iter;
-        const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
+        const int c0 = (tile0 + s * a.CS) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         const int nb = boxes_of(it);
         for (int b = 0; b < nb; ++b) l2_tma_prefetch(&tmap, c0, r0 + b * kL2BoxRows);
       };
@@ -348,7 +354,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         const int nb = boxes_of(it);
         const uint32_t bar = full0 + 8 * stage;
         l2_mbar_expect_tx(bar, nb * kL2BoxBytes);
-        const int c0 = (s * a.CS + rank) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
+        const int c0 = (tile0 + s * a.CS) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         for (int b = 0; b < nb; ++b)
           l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, c0, r0 + b * kL2BoxRows, bar);
         // L2 prefetch runs a.prefetch items ahead of the ring (the ring itself holds `stages`)
@@ -386,7 +392,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       caddr[v] = l2_smem(ring) + (uint32_t)tid * kL2Tile + (((v + lc) & 3) << 4) + 8 * lh;
     // x: this thread's word of the B-fragment layout
     constexpr int XW = l2_x_words<D>();
-    int xoff = tid < XW ? l2_x_offset<D>(tid, rank, a.M) : -1;
+    int xoff = tid < XW ? l2_x_offset<D>(tid, tile0, a.M) : -1;
     int xstep = a.CS * (kL2Tile / a.M) * D;        // elements between this CTA's consecutive tiles
     const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
     uint32_t* xs_mine = reinterpret_cast<uint32_t*>(xs) + tid;
@@ -471,6 +477,20 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         if (s == 0 && it == 0) l2_trace(a, 9);
       }
     }
+    if (my_tiles == 0) {                           // no tile in this K group: contribute zeros
+      if (clustered) {
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+        for (int i = tid; i < rows; i += kL2Cons) {
+          const int o = i / chunk, j = i - o * chunk;
+          uint32_t ra;
+          const uint32_t la = recv_addr + (uint32_t)(rank * chunk + j) * 4u;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(la), "r"(o));
+          asm volatile("st.shared::cluster.f32 [%0], %1;" :: "r"(ra), "f"(0.f) : "memory");
+        }
+      } else {
+        for (int i = tid; i < rows; i += kL2Cons) rowsum[i] = 0.f;
+      }
+    }
     l2_trace(a, 5);
   }
 
@@ -496,7 +516,39 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     }
     float sum = 0.f;
     for (int r = 0; r < fin_parts; ++r) sum += fin[r * part_stride + i + fin_off];
-    reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+    if (a.KG == 1)
+      reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+    else
+      __stcg(a.ws_part + ((size_t)tok * a.KG + kg) * a.N + row, sum);
+  }
+  // ---- split-K over the K groups (KG > 1): partial sums meet in the workspace; the last of the KG
+  // CTAs that share these rows (a ticket) adds them in K-group order - deterministic - and stores ----
+  if (a.KG > 1) {
+    int* last_flag = reinterpret_cast<int*>(bars + 2 * kL2MaxStages);
+    __threadfence();
+    __syncthreads();
+    int* ticket = a.ws_tickets + ((size_t)tok * gridDim.x / (a.CS * a.KG) + block) * a.CS + rank;
+    if (tid == 0) {
+      const int t = atomicAdd(ticket, 1);
+      *last_flag = (t == a.KG - 1);
+      if (t == a.KG - 1) *ticket = 0;              // leave the counter zero for the next launch
+    }
+    __syncthreads();
+    if (*last_flag) {
+      __threadfence();
+      for (int i = fin0 + tid; i < fin1; i += kL2Threads) {
+        const int row = rb.row0 + i;
+        float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
+        float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
+        if (i != fin0 + tid) {
+          sc = Traits<T>::to_f(reinterpret_cast<const T*>(a.scales)[row]);
+          b = a.bias ? Traits<T>::to_f(reinterpret_cast<const T*>(a.bias)[row]) : 0.f;
+        }
+        float sum = 0.f;
+        for (int g = 0; g < a.KG; ++g) sum += __ldcg(a.ws_part + ((size_t)tok * a.KG + g) * a.N + row);
+        reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+      }
+    }
   }
   l2_trace(a, 7);
 }
@@ -507,12 +559,12 @@ extern unsigned long long* g_lut_trace;
 extern int g_lut_last_grid[4];
 
 struct Lut2Plan {
-  int cs, S, n_tiles, rows_per_cluster, stages, smem_cb, smem_x, smem_total;
+  int cs, S, kg, n_tiles, rows_per_cluster, stages, smem_cb, smem_x, smem_total;
 };
 
 static int lut2_smem_bytes(int E, int stages, int smem_cb, int smem_x, int rows) {
   return E * kL2Tile * 4 + stages * kL2StageBytes + smem_cb + smem_x + (2 * rows + kL2MaxCluster) * 4 +
-         2 * 8 * kL2MaxStages;
+         2 * 8 * kL2MaxStages + 16;                // mbarriers + the K-group ticket flag
 }
 
 constexpr int kL2TwoPerSm = 113 * 1024;            // two CTAs (this layer's + the next layer's) fit one SM
@@ -554,9 +606,14 @@ static int64_t lut2_blocks(const int64_t* part_sizes, int n_parts, int64_t n, in
   return b;
 }
 
-// Cluster size and rows per cluster from a small cycle model: a CTA pays a fixed cost, one table
-// build per tile and 64 lookups per (tile, row); one CTA of this launch per SM where possible
-// (the second slot belongs to the next layer under programmatic dependent launch).
+constexpr int kL2MaxKG = 8;                        // K groups (clusters along K) per row block
+constexpr int kL2TicketBytes = 64 * 1024;          // head of the workspace (include/pq_b200.h)
+
+// Cluster size CS, tiles per CTA S, K groups KG (CS * S * KG >= n_tiles) and rows per row block
+// from a small cycle model calibrated on B200 phase traces (profiles/r1_1x_trace_lut_tma*.txt):
+// a CTA pays a fixed cost, ~2500 cycles per table build and ~1900 per 512-row iteration of
+// lookups; a cluster reduce costs ~1200, the cross-cluster (workspace + ticket) reduce ~3000.
+// One CTA per SM (16 + 1 warps, > 113 KiB of shared memory).
 static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
                       const int64_t* part_sizes, int n_parts) {
   const int E = 1 << nbits;
@@ -564,46 +621,57 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
   pl.n_tiles = (int)((gp + kL2Tile - 1) / kL2Tile);
   pl.smem_cb = m * E * d * 2;
   static const int force_cs = [] { const char* e = getenv("PQ_LUT2_CS"); return e ? atoi(e) : 0; }();
+  static const int force_kg = [] { const char* e = getenv("PQ_LUT2_KG"); return e ? atoi(e) : 0; }();
   static const int force_stages = [] { const char* e = getenv("PQ_LUT2_STAGES"); return e ? atoi(e) : 0; }();
-  static const int force_clusters = [] { const char* e = getenv("PQ_LUT2_CLUSTERS"); return e ? atoi(e) : 0; }();
   const int sms = sm_count();
   double best = 1e30;
   bool found = false;
   for (int cs = 1; cs <= kL2MaxCluster; cs *= 2) {
     if (cs > pl.n_tiles) break;
     if (force_cs && cs != force_cs) continue;
-    const int S = (pl.n_tiles + cs - 1) / cs;
-    const int smem_x = S * (d == 16 ? 512 : 256) * 4;      // B-fragment order, see l2_stage_x
-    if (smem_x > 32 * 1024) continue;
     int slots1 = lut2_cluster_slots(cs, 200 * 1024);           // one CTA per SM
     if (slots1 * cs > sms) slots1 = sms / cs;
-    int target = force_clusters ? force_clusters : slots1 / (int)t;
-    if (target < 1) target = 1;
-    int rows = (int)((n + target - 1) / target);
-    rows = (rows + kL2BoxRows - 1) / kL2BoxRows * kL2BoxRows;
-    const int max_rows = 4096;
-    if (rows > max_rows) rows = max_rows;
-    while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
-    const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
-    int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(kL2MaxStages, max(2, S * n_iter));
-    auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, pl.smem_cb, smem_x, rows); };
-    while (stages > 2 && smem_of(stages) > 220 * 1024) --stages;
-    const int smem = smem_of(stages);
-    if (smem > 220 * 1024) continue;
-    const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, rows) * t;
-    const int slots = lut2_cluster_slots(cs, smem);
-    const int64_t waves = (blocks + slots - 1) / slots;
-    const double crowd = blocks > slots1 ? 1.6 : 1.0;          // two CTAs of this launch share an SM
-    const double cta = 3000.0 + (cs > 1 ? 1200.0 : 0.0) +
-                       crowd * S * (700.0 * E / 256.0 + n_iter * 1024.0 * 1.3);
-    const double cost = (double)waves * cta;
-    if (cost < best) {
-      best = cost; found = true;
-      pl.cs = cs; pl.S = S; pl.rows_per_cluster = rows; pl.stages = stages; pl.smem_x = smem_x;
-      pl.smem_total = smem;
+    for (int kg = 1; kg <= kL2MaxKG; ++kg) {
+      if (force_kg && kg != force_kg) continue;
+      const int S = (pl.n_tiles + cs * kg - 1) / (cs * kg);
+      if ((kg - 1) * cs * S >= pl.n_tiles) continue;           // the last K group would be empty
+      const int smem_x = S * (d == 16 ? 512 : 256) * 4;        // B-fragment order, see l2_x_offset
+      if (smem_x > 32 * 1024) continue;
+      int target = slots1 / (int)(t * kg);                     // row blocks in one wave
+      if (target < 1) target = 1;
+      int rows = (int)((n + target - 1) / target);
+      rows = (rows + kL2BoxRows - 1) / kL2BoxRows * kL2BoxRows;
+      const int max_rows = 4096;
+      if (rows > max_rows) rows = max_rows;
+      while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
+      const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
+      int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(kL2MaxStages, max(2, S * n_iter));
+      auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, pl.smem_cb, smem_x, rows); };
+      while (stages > 2 && smem_of(stages) > 220 * 1024) --stages;
+      const int smem = smem_of(stages);
+      if (smem > 220 * 1024) continue;
+      const int64_t clusters = lut2_blocks(part_sizes, n_parts, n, rows) * kg * t;
+      if (clusters * cs > 65535 * 8) continue;
+      const int64_t waves = (clusters + slots1 - 1) / slots1;
+      // narrower clusters stream narrower strips of the code matrix and measured ~20 % slower per
+      // row iteration; K groups only where they clearly pay (profiles/r1_18_microbench_lut_tma.jsonl)
+      const double item = 1900.0 * (cs < 8 ? 1.2 : 1.0);
+      const double cta = 5000.0 + (cs > 1 ? 1200.0 : 0.0) + (kg > 1 ? 3000.0 : 0.0) +
+                         S * (2500.0 * E / 256.0 + (rows / 512.0 + 0.3) * item);
+      const double cost = (double)waves * cta * (kg > 1 ? 1.15 : 1.0);
+      if (cost < best) {
+        best = cost; found = true;
+        pl.cs = cs; pl.S = S; pl.kg = kg; pl.rows_per_cluster = rows; pl.stages = stages;
+        pl.smem_x = smem_x; pl.smem_total = smem;
+      }
     }
   }
   return found;
+}
+
+// Upper bound for every plan (the plan may depend on the partition sizes): tickets + KG partials.
+int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t, int, int, int, int) {
+  return kL2TicketBytes + (int64_t)kL2MaxKG * t * n * 4;
 }
 
 bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
@@ -668,7 +736,7 @@ static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, 
     attr_set[dev & 63] = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.cs, a.T, 1);
+  cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.kg * pl.cs, a.T, 1);
   cfg.blockDim = dim3(kL2Threads);
   cfg.dynamicSmemBytes = pl.smem_total;
   cfg.stream = stream;
@@ -702,7 +770,8 @@ static int launch_lut2_d(const CUtensorMap& map, Lut2Args& a, int d, const Lut2P
 int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
                        const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
                        int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
-                       int n_parts, int dtype, cudaStream_t stream) {
+                       int n_parts, int dtype, void* workspace, int64_t workspace_bytes,
+                       cudaStream_t stream) {
   if ((uintptr_t)codes % 16 || (uintptr_t)x % 4 || (x_stride * 2) % 4) return PQ_ERR_ALIGN;
   Lut2Plan pl;
   if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts)) return PQ_ERR_UNSUPPORTED;
@@ -711,7 +780,15 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
   a.Gp = (int)(k / d * m); a.n_tiles = pl.n_tiles; a.S = pl.S; a.CS = pl.cs;
-  a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages;
+  a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages; a.KG = pl.kg;
+  if (pl.kg > 1) {
+    const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster);
+    if (!workspace || workspace_bytes < kL2TicketBytes + (int64_t)pl.kg * t * n * 4 ||
+        t * blocks * pl.cs * 4 > kL2TicketBytes)
+      return PQ_ERR_WORKSPACE;
+    a.ws_tickets = reinterpret_cast<int*>(workspace);
+    a.ws_part = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + kL2TicketBytes);
+  }
   static const int prefetch = [] { const char* e = getenv("PQ_LUT2_PREFETCH"); return e ? atoi(e) : 8; }();
   a.prefetch = prefetch;
 
