@@ -1,12 +1,9 @@
 set -x
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_ref_cuda.py -x -q 2>&1 | tail -3
-timeout 600 python tools/microbench.py --shapes qkv7b,o7b,gateup7b,down7b,gateup70b,down70b --formats 8x8x1,8x8x2 --tokens 1 --algos lut2 --pdl 1 --dequant 0 > gpurun_out/r1_19_microbench_lut2.jsonl 2>&1; echo "microbench rc=$?"
-python - <<'PY'
-import ast
-for l in open('gpurun_out/r1_19_microbench_lut2.jsonl'):
-    l=l.strip()
-    if l.startswith('{'):
-        d=ast.literal_eval(l); print(d['shape'],d['fmt'],d['algo'],'us=%.1f gbs=%.0f'%(d['us'],d['gbs']))
-    else: print(l)
-PY
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/r1_20_pytest_gpu.log 2>&1; echo "pytest rc=$?"
+tail -4 gpurun_out/r1_20_pytest_gpu.log
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -4
+timeout 600 python bench.py > gpurun_out/r1_20_bench.json 2> gpurun_out/r1_20_bench.err; echo "bench rc=$?"
+cat gpurun_out/r1_20_bench.json
+timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu > /dev/null 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:pq_ -c 1200 --csv --log-file gpurun_out/r1_20_ncu_launches_bench.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/r1_20_ncu_launches.log 2>&1; echo "ncu launches rc=$?"
+tail -2 gpurun_out/r1_20_ncu_launches.log
