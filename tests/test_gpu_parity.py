@@ -116,10 +116,13 @@ LUT_TMA_SWEEP = [(8, 8, 1), (8, 8, 2), (8, 8, 4), (4, 8, 1), (6, 8, 2), (8, 4, 1
 @pytest.mark.parametrize("fmt", LUT_TMA_SWEEP)
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize("t", [1, 2, 5, 8])
-@pytest.mark.parametrize("shape", [([128, 64, 72], 64), ([65], 80), ([1024, 48], 256), ([200], 96), ([2500, 700], 144)])
+@pytest.mark.parametrize("shape", [([128, 64, 72], 64), ([65], 80), ([1024, 48], 256), ([200], 96), ([2500, 700], 144),
+                                   ([1024, 512], 86), ([4096], 344), ([704], 172)])
 def test_gemm_lut_tma_sweep(fmt, dtype, t, shape):
     """TMA-fed table GEMV (pq_gemv_lut2.cu): ragged partitions and row blocks that are not a
-    multiple of the 64-row box, K that ends inside a 64-position tile or a 16-byte chunk, every
+    multiple of the 64-row box, K that ends inside a 64-position tile or a 16-byte chunk, code
+    pitches that are not a multiple of 16 bytes (TMA super-rows of 2, 4, 8 rows - the TP = 4 / 8
+    shards of down_proj), every
     cluster size the planner picks (1..8 tiles and more), several tiles per CTA, masked codes
     (nbits < 8), 1..8 tokens on grid.y; reproducible bit for bit."""
     b, d, m = fmt
@@ -127,7 +130,7 @@ def test_gemm_lut_tma_sweep(fmt, dtype, t, shape):
     k = groups * d
     n = sum(parts)
     if not _lib.load().pq_b200_algo_supported(_lib.ALGO_GEMV_LUT_TMA, t, n, k, d, b, m):
-        pytest.skip("code bytes per row not a multiple of 16")
+        pytest.skip("shape outside the TMA kernel (odd pitch with too few rows)")
     c = O.make_case(parts, k, b, d, m, t=t, dtype=dtype, seed=7 + t, bias=(t % 2 == 0))
     g = dev(c)
     y = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)

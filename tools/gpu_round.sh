@@ -1,9 +1,9 @@
 set -x
 mkdir -p gpurun_out
-timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/r1_20_pytest_gpu.log 2>&1; echo "pytest rc=$?"
-tail -4 gpurun_out/r1_20_pytest_gpu.log
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -4
-timeout 600 python bench.py > gpurun_out/r1_20_bench.json 2> gpurun_out/r1_20_bench.err; echo "bench rc=$?"
-cat gpurun_out/r1_20_bench.json
-timeout 300 python bench.py --steps 3 --warmup 3 --no-cpu > /dev/null 2>&1 && timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:pq_ -c 1200 --csv --log-file gpurun_out/r1_20_ncu_launches_bench.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/r1_20_ncu_launches.log 2>&1; echo "ncu launches rc=$?"
-tail -2 gpurun_out/r1_20_ncu_launches.log
+N=$1
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/tp_check.py > gpurun_out/r1_23_tp_check_$N.log 2>&1; echo "tp_check rc=$?"
+grep -E "tp$N|TP_CHECK|Error|error" gpurun_out/r1_23_tp_check_$N.log | tail -8
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/r1_23_bench_tp$N.json 2> gpurun_out/r1_23_bench_tp$N.err; echo "bench tp rc=$?"
+python -c "
+import json,sys
+d=json.loads([l for l in open('gpurun_out/r1_23_bench_tp$N.json') if l.startswith('{')][0]); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value']); print({k:(round(v['us'],2),round(v['gbs'])) for k,v in d['kernels'].items()})"

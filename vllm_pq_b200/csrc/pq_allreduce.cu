@@ -21,6 +21,8 @@
 
 namespace pq {
 
+extern bool g_use_pdl;
+
 constexpr int kArThreads = 512;
 constexpr int kArMaxBlocks = 36;
 // flag buffer layout (uint32 words): [block * world + peer] ... then
@@ -45,6 +47,11 @@ template <typename T, int WORLD>
 __global__ void __launch_bounds__(kArThreads)
 pq_allreduce_oneshot_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int n_vec,
                             ArPeers peers, int rank, long long slot_bytes) {
+  // Programmatic dependent launch: the next layer's GEMV may start its weight prefetch now; this
+  // kernel itself must not touch anything (not even its epoch counter, which the previous
+  // all-reduce two launches back advances at its very end) before the GEMV it follows is complete.
+  pdl_launch_dependents();
+  pdl_wait();
   uint32_t* my_flags = peers.flags[rank];
   const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(my_flags + kArCounterWord) + 1u;
   const long long slot_off = (long long)(epoch & 1u) * WORLD * slot_bytes;
@@ -107,9 +114,16 @@ static int launch_ar(const void* in, void* out, int n_vec, const ArPeers& peers,
   int blocks = (n_vec + kArThreads - 1) / kArThreads;
   if (blocks > kArMaxBlocks) blocks = kArMaxBlocks;
   if (blocks < 1) blocks = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(kArThreads); cfg.dynamicSmemBytes = 0; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 1 : 0;
+  int rc = 0;
 #define PQ_AR(W)                                                                              \
-  pq_allreduce_oneshot_kernel<T, W><<<blocks, kArThreads, 0, stream>>>(                       \
-      (const uint4*)in, (uint4*)out, n_vec, peers, rank, slot_bytes)
+  rc = (int)cudaLaunchKernelEx(&cfg, pq_allreduce_oneshot_kernel<T, W>, (const uint4*)in,     \
+                               (uint4*)out, n_vec, peers, rank, (long long)slot_bytes)
   switch (world) {
     case 2: PQ_AR(2); break;
     case 4: PQ_AR(4); break;
@@ -117,7 +131,7 @@ static int launch_ar(const void* in, void* out, int n_vec, const ArPeers& peers,
     default: return PQ_ERR_UNSUPPORTED;
   }
 #undef PQ_AR
-  return (int)cudaGetLastError();
+  return rc;
 }
 
 int allreduce_oneshot_dispatch(const void* in, void* out, int64_t n_elems, int dtype,

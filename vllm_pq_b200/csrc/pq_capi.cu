@@ -94,16 +94,17 @@ int pq_b200_dequant(const void* codes, const void* codebooks, const void* scales
                               dtype, (cudaStream_t)stream);
 }
 
-int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+static int pick_algo_impl(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, bool allow_lut_tma) {
   // Crossovers measured on B200 (profiles/r1_03_*): the register-fragment mma.sync kernel wins for
   // 2..16 tokens everywhere and at 1 token / 32-64 tokens on the small-N layers (o_proj, down_proj),
   // where the table GEMV's per-CTA table build and the tcgen05 kernel's per-tile dequant are not
   // amortised.  Tuning knobs: PQ_T1_ALGO forces the batch-1 kernel, PQ_MMA_MAX_T caps the mma range.
   static const int t1_algo = [] { const char* e = getenv("PQ_T1_ALGO"); return e ? atoi(e) : 0; }();
   static const int mma_max_t = [] { const char* e = getenv("PQ_MMA_MAX_T"); return e ? atoi(e) : 64; }();
-  if (t == 1 && t1_algo && pq_b200_algo_supported(t1_algo, t, n, k, d, nbits, m)) return t1_algo;
+  if (t == 1 && t1_algo && (allow_lut_tma || t1_algo != PQ_ALGO_GEMV_LUT_TMA) &&
+      pq_b200_algo_supported(t1_algo, t, n, k, d, nbits, m)) return t1_algo;
   // one token: the TMA-fed table GEMV wins on every Llama projection (profiles/r1_13_microbench_lut2.jsonl)
-  if (t == 1 && pq::gemv_lut2_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT_TMA;
+  if (allow_lut_tma && t == 1 && pq::gemv_lut2_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT_TMA;
   const bool mma_ok = t <= mma_max_t && pq::gemm_mma_supported(t, n, k, d, nbits, m);
   if (mma_ok) {
     if (t >= 2 && t <= 16) return PQ_ALGO_GEMM_MMA;
@@ -114,6 +115,10 @@ int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) 
   if (pq::gemv_lut_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
   if (mma_ok) return PQ_ALGO_GEMM_MMA;
   return PQ_ALGO_GEMV_DIRECT;
+}
+
+int pq_b200_pick_algo(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  return pick_algo_impl(t, n, k, d, nbits, m, true);
 }
 
 int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
@@ -147,8 +152,17 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
   if (!x || !codes || !codebooks || !scales || !y) return PQ_ERR_NULL;
   if (t <= 0 || t > INT32_MAX || x_stride < k || y_stride < n) return PQ_ERR_SHAPE;
   if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
-  if (algo == PQ_ALGO_AUTO) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
+  const bool was_auto = algo == PQ_ALGO_AUTO;
+  if (was_auto) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
   cudaStream_t s = (cudaStream_t)stream;
+  if (was_auto && algo == PQ_ALGO_GEMV_LUT_TMA) {
+    // the one condition only the dispatcher can see: partition sizes that are not a multiple of
+    // the TMA super-row (odd row counts with an odd code pitch) - fall back to the other kernels
+    rc = pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
+                                nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+    if (rc != PQ_ERR_UNSUPPORTED) return rc;
+    algo = pick_algo_impl(t, n, k, d, nbits, m, false);
+  }
   switch (algo) {
     case PQ_ALGO_GEMV_DIRECT:
       return pq::gemv_direct_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k,

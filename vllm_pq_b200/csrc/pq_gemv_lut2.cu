@@ -58,6 +58,10 @@ struct Lut2Args {
   long long x_stride, y_stride;
   int T, N, K, E, M;
   int Gp;                 // positions (= code bytes) per row
+  int R;                  // rows per TMA super-row (always 1: TMA rejects boxes that do not start on 16 bytes)
+  const unsigned char* codes;
+  int copy_w;             // 0: TMA.  4 / 8: the code pitch is not a multiple of 16 bytes (TP shards of
+                          // down_proj) - the producer warp copies with cp.async of this width instead
   int n_tiles;            // ceil(Gp / 64)
   int S;                  // tiles per CTA = ceil(n_tiles / CS)
   int CS;                 // cluster size
@@ -325,7 +329,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
 
   if (tid == 0) {
     for (int i = 0; i < a.stages; ++i) {
-      l2_mbar_init(full0 + 8 * i, 1);
+      l2_mbar_init(full0 + 8 * i, a.copy_w ? 32 : 1);
       l2_mbar_init(empty0 + 8 * i, kL2ConsWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -336,16 +340,50 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   if (warp == kL2ConsWarps) {
     // ================= producer warp: the whole code stream of this CTA, weights only ===========
     pdl_launch_dependents();
-    if (lane == 0) {
+    if (a.copy_w) {
+      // ---- code pitch not a multiple of 16 bytes: no TMA.  All 32 lanes copy the item's
+      // [512 rows][64 B] with cp.async (8 or 4 bytes; consecutive lanes = consecutive bytes of a row)
+      // and arrive on the stage's barrier when their copies land.  Bytes beyond the row / the
+      // matrix are not copied: their table columns are all zero (x is zero beyond K) and rows
+      // beyond the block are never used.
       const uint32_t ring_addr = l2_smem(ring);
+      const int w = a.copy_w, per_row = kL2Tile / w;
+      int stage = 0, round = 0;
+      for (int i = 0; i < total; ++i) {
+        const int s = i / n_iter, it = i - s * n_iter;
+        if (round > 0) l2_mbar_wait(empty0 + 8 * stage, (round - 1) & 1);
+        const int col0 = (tile0 + s * a.CS) * kL2Tile;
+        const int nrow = min(kL2Cons, rows - it * kL2Cons);
+        const unsigned char* src = a.codes + (size_t)(rb.row0 + it * kL2Cons) * a.Gp + col0;
+        const uint32_t dst = ring_addr + stage * kL2StageBytes;
+        for (int idx = lane; idx < nrow * per_row; idx += 32) {
+          const int r = idx / per_row, c = (idx - r * per_row) * w;
+          if (col0 + c + w <= a.Gp) {
+            if (w == 8)
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst + r * kL2Tile + c), "l"(src + (size_t)r * a.Gp + c) : "memory");
+            else
+              asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst + r * kL2Tile + c), "l"(src + (size_t)r * a.Gp + c) : "memory");
+          }
+        }
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(full0 + 8 * stage) : "memory");
+        if (++stage == a.stages) { stage = 0; ++round; }
+      }
+      asm volatile("cp.async.wait_all;" ::: "memory");
+    } else if (lane == 0) {
+      const uint32_t ring_addr = l2_smem(ring);
+      // A box is 64 code bytes x 64 super-rows; a super-row is R consecutive rows (the TMA row pitch
+      // must be a multiple of 16 bytes), so box b of an item holds the rows = (b % R) mod R of the
+      // (b / R)-th group of 64 R rows; the consumers undo the interleave (`perm`).
+      const int R = a.R, grp_rows = kL2BoxRows * R;
       auto boxes_of = [&](int it) {
-        return min(kL2StageBoxes, (rows - it * kL2Cons + kL2BoxRows - 1) / kL2BoxRows);
+        return min(kL2StageBoxes, (rows - it * kL2Cons + grp_rows - 1) / grp_rows * R);
       };
+      auto box_c0 = [&](int s, int b) { return (tile0 + s * a.CS) * kL2Tile + (b % R) * a.Gp; };
+      auto box_r0 = [&](int it, int b) { return (rb.row0 + it * kL2Cons) / R + (b / R) * kL2BoxRows; };
       auto prefetch_item = [&](int i) {
         const int s = i / n_iter, it = i - s * n_iter;
-        const int c0 = (tile0 + s * a.CS) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         const int nb = boxes_of(it);
-        for (int b = 0; b < nb; ++b) l2_tma_prefetch(&tmap, c0, r0 + b * kL2BoxRows);
+        for (int b = 0; b < nb; ++b) l2_tma_prefetch(&tmap, box_c0(s, b), box_r0(it, b));
       };
       int stage = 0, round = 0;
       for (int i = 0; i < total; ++i) {
@@ -354,9 +392,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         const int nb = boxes_of(it);
         const uint32_t bar = full0 + 8 * stage;
         l2_mbar_expect_tx(bar, nb * kL2BoxBytes);
-        const int c0 = (tile0 + s * a.CS) * kL2Tile, r0 = rb.row0 + it * kL2Cons;
         for (int b = 0; b < nb; ++b)
-          l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, c0, r0 + b * kL2BoxRows, bar);
+          l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, box_c0(s, b), box_r0(it, b), bar);
         // L2 prefetch runs a.prefetch items ahead of the ring (the ring itself holds `stages`)
         if (i == 0)
           for (int j = a.stages; j < min(total, a.stages + a.prefetch); ++j) prefetch_item(j);
@@ -383,6 +420,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       colv[v][0] = cbase + (64u * lh) * 0x01010101u;
       colv[v][1] = cbase + (64u * (lh ^ 1)) * 0x01010101u;
     }
+    // row (inside the iteration) of the ring slot this thread reads: box tid / 64, line tid % 64
+    int perm = ((tid >> 6) / a.R) * (kL2BoxRows * a.R) + (tid & 63) * a.R + ((tid >> 6) % a.R);
     uint32_t lut_base = l2_smem(lut);
     uint32_t emask4 = ((uint32_t)a.E - 1u) * 0x01010101u;
     uint32_t recv_addr = l2_smem(recv);
@@ -403,13 +442,13 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     for (int i = 0; i < 4; ++i) {
       asm volatile("" : "+r"(sel[i]), "+r"(colv[i][0]), "+r"(colv[i][1]), "+r"(caddr[i]));
     }
-    asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xoff), "+r"(xstep), "+l"(xg), "+l"(xs_mine));
+    asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xoff), "+r"(xstep), "+r"(perm), "+l"(xg), "+l"(xs_mine));
 
     // codes of one item (row iteration `it` of a tile) -> registers; the stage is released at once
     int stage = 0, round = 0;
     auto load_codes = [&](uint32_t (&cw)[4][4], int it) {
       l2_mbar_wait(full0 + 8 * stage, round & 1);
-      if (it * kL2Cons + tid < rows) {
+      if (it * kL2Cons + perm < rows) {
         const uint32_t so = stage * kL2StageBytes;
 #pragma unroll
         for (int v = 0; v < 4; ++v) {
@@ -424,7 +463,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     // 64 lookups of one row; on the CTA's last tile the row's partial sum goes straight to the
     // CTA that finishes the row (distributed shared memory), else it is kept in rowsum
     auto lookups = [&](const uint32_t (&cw)[4][4], int s, int it) {
-      const int row_l = it * kL2Cons + tid;
+      const int row_l = it * kL2Cons + perm;
       if (row_l < rows) {
         float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -680,7 +719,7 @@ bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int 
   if (m != 1 && m != 2 && m != 4) return false;
   if (k % d) return false;
   const int64_t gp = k / d * m;
-  if (gp % 16 || gp < kL2Tile || n < kL2BoxRows) return false;        // TMA: 16-byte row pitch, box inside the tensor
+  if (gp % 4 || gp < kL2Tile || n < kL2BoxRows) return false;          // TMA box inside the tensor; cp.async >= 4 bytes
   if (gp > (int64_t)1 << 30 || n > (int64_t)1 << 30) return false;
   Lut2Plan pl;
   return lut2_plan(pl, t, n, k, d, nbits, m, nullptr, PQ_MAX_PARTS);
@@ -711,11 +750,11 @@ static PFN_l2TmapEncodeTiled lut2_tmap_encoder() {
 
 // codes [N, Gp] bytes, row-major, as a 2-D tensor map: box = 64 code bytes x 64 rows, no swizzle,
 // out-of-bounds rows and positions read as zero.
-static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64_t gp) {
+static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64_t gp, int R) {
   PFN_l2TmapEncodeTiled enc = lut2_tmap_encoder();
   if (!enc) return PQ_ERR_UNSUPPORTED;
-  const cuuint64_t gdim[2] = {(cuuint64_t)gp, (cuuint64_t)n};
-  const cuuint64_t gstride[1] = {(cuuint64_t)gp};
+  const cuuint64_t gdim[2] = {(cuuint64_t)(gp * R), (cuuint64_t)(n / R)};
+  const cuuint64_t gstride[1] = {(cuuint64_t)(gp * R)};
   const cuuint32_t box[2] = {(cuuint32_t)kL2Tile, (cuuint32_t)kL2BoxRows};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(codes), gdim, gstride, box, estr,
@@ -779,7 +818,10 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.x = x; a.codebooks = codebooks; a.scales = scales; a.bias = bias;
   a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
-  a.Gp = (int)(k / d * m); a.n_tiles = pl.n_tiles; a.S = pl.S; a.CS = pl.cs;
+  a.Gp = (int)(k / d * m); a.R = 1; a.n_tiles = pl.n_tiles;
+  a.codes = (const unsigned char*)codes;
+  a.copy_w = a.Gp % 16 == 0 ? 0 : (a.Gp % 8 == 0 ? 8 : 4);
+  a.S = pl.S; a.CS = pl.cs;
   a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages; a.KG = pl.kg;
   if (pl.kg > 1) {
     const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster);
@@ -797,7 +839,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
   if (rc) return rc;
   CUtensorMap map;
-  rc = lut2_codes_tmap(&map, codes, n, a.Gp);
+  rc = lut2_codes_tmap(&map, codes, n, a.copy_w ? (a.Gp + 15) / 16 * 16 : a.Gp, 1);   // unused when copy_w
   if (rc) return rc;
   return dtype == PQ_F16 ? launch_lut2_d<__half>(map, a, d, pl, stream)
                          : launch_lut2_d<__nv_bfloat16>(map, a, d, pl, stream);
