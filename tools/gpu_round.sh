@@ -1,9 +1,12 @@
 set -x
 mkdir -p gpurun_out
-N=$1
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/tp_check.py > gpurun_out/r1_23_tp_check_$N.log 2>&1; echo "tp_check rc=$?"
-grep -E "tp$N|TP_CHECK|Error|error" gpurun_out/r1_23_tp_check_$N.log | tail -8
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 30 --warmup 5 > gpurun_out/r1_23_bench_tp$N.json 2> gpurun_out/r1_23_bench_tp$N.err; echo "bench tp rc=$?"
-python -c "
-import json,sys
-d=json.loads([l for l in open('gpurun_out/r1_23_bench_tp$N.json') if l.startswith('{')][0]); print(d['n_gpus'], d['value'], d['ms_per_step'], d['e2e']['value']); print({k:(round(v['us'],2),round(v['gbs'])) for k,v in d['kernels'].items()})"
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_lut_tma_kgroups.py -x -q -k "lut_tma" 2>&1 | tail -3
+timeout 600 python tools/microbench.py --shapes qkv7b,o7b,gateup7b,down7b,gateup70b,down70b --formats 8x8x1,8x8x2 --tokens 1 --algos auto --pdl 1 --dequant 0 > gpurun_out/r1_25_microbench_lut2.jsonl 2>&1; echo "microbench rc=$?"
+python - <<'PY'
+import ast
+for l in open('gpurun_out/r1_25_microbench_lut2.jsonl'):
+    l=l.strip()
+    if l.startswith('{'):
+        d=ast.literal_eval(l); print(d['shape'],d['fmt'],d['algo'],'us=%.1f gbs=%.0f'%(d['us'],d['gbs']))
+    else: print(l)
+PY

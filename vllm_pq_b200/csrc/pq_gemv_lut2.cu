@@ -371,15 +371,11 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       asm volatile("cp.async.wait_all;" ::: "memory");
     } else if (lane == 0) {
       const uint32_t ring_addr = l2_smem(ring);
-      // A box is 64 code bytes x 64 super-rows; a super-row is R consecutive rows (the TMA row pitch
-      // must be a multiple of 16 bytes), so box b of an item holds the rows = (b % R) mod R of the
-      // (b / R)-th group of 64 R rows; the consumers undo the interleave (`perm`).
-      const int R = a.R, grp_rows = kL2BoxRows * R;
       auto boxes_of = [&](int it) {
-        return min(kL2StageBoxes, (rows - it * kL2Cons + grp_rows - 1) / grp_rows * R);
+        return min(kL2StageBoxes, (rows - it * kL2Cons + kL2BoxRows - 1) / kL2BoxRows);
       };
-      auto box_c0 = [&](int s, int b) { return (tile0 + s * a.CS) * kL2Tile + (b % R) * a.Gp; };
-      auto box_r0 = [&](int it, int b) { return (rb.row0 + it * kL2Cons) / R + (b / R) * kL2BoxRows; };
+      auto box_c0 = [&](int s, int) { return (tile0 + s * a.CS) * kL2Tile; };
+      auto box_r0 = [&](int it, int b) { return rb.row0 + it * kL2Cons + b * kL2BoxRows; };
       auto prefetch_item = [&](int i) {
         const int s = i / n_iter, it = i - s * n_iter;
         const int nb = boxes_of(it);
@@ -394,10 +390,11 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         l2_mbar_expect_tx(bar, nb * kL2BoxBytes);
         for (int b = 0; b < nb; ++b)
           l2_tma_load(ring_addr + stage * kL2StageBytes + b * kL2BoxBytes, &tmap, box_c0(s, b), box_r0(it, b), bar);
-        // L2 prefetch runs a.prefetch items ahead of the ring (the ring itself holds `stages`)
-        if (i == 0)
-          for (int j = a.stages; j < min(total, a.stages + a.prefetch); ++j) prefetch_item(j);
-        else if (i + a.stages + a.prefetch - 1 < total) prefetch_item(i + a.stages + a.prefetch - 1);
+        // L2 prefetch runs a.prefetch items ahead of the ring (the ring itself holds `stages`); the
+        // first burst goes out only after the ring's own loads (a TMA issue costs ~70 cycles)
+        if (i == min(total, a.stages) - 1)
+          for (int j = a.stages; j < min(total, i + a.stages + a.prefetch); ++j) prefetch_item(j);
+        else if (i >= a.stages && i + a.stages + a.prefetch - 1 < total) prefetch_item(i + a.stages + a.prefetch - 1);
         if (++stage == a.stages) { stage = 0; ++round; }
       }
     }
@@ -420,8 +417,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       colv[v][0] = cbase + (64u * lh) * 0x01010101u;
       colv[v][1] = cbase + (64u * (lh ^ 1)) * 0x01010101u;
     }
-    // row (inside the iteration) of the ring slot this thread reads: box tid / 64, line tid % 64
-    int perm = ((tid >> 6) / a.R) * (kL2BoxRows * a.R) + (tid & 63) * a.R + ((tid >> 6) % a.R);
+    // row (inside the iteration) of the ring slot this thread reads
+    int perm = tid;
     uint32_t lut_base = l2_smem(lut);
     uint32_t emask4 = ((uint32_t)a.E - 1u) * 0x01010101u;
     uint32_t recv_addr = l2_smem(recv);
