@@ -1,12 +1,8 @@
 set -x
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_lut_tma_kgroups.py -x -q -k "lut_tma" 2>&1 | tail -3
-timeout 600 python tools/microbench.py --shapes qkv7b,o7b,gateup7b,down7b,gateup70b,down70b --formats 8x8x1,8x8x2 --tokens 1 --algos auto --pdl 1 --dequant 0 > gpurun_out/r1_25_microbench_lut2.jsonl 2>&1; echo "microbench rc=$?"
-python - <<'PY'
-import ast
-for l in open('gpurun_out/r1_25_microbench_lut2.jsonl'):
-    l=l.strip()
-    if l.startswith('{'):
-        d=ast.literal_eval(l); print(d['shape'],d['fmt'],d['algo'],'us=%.1f gbs=%.0f'%(d['us'],d['gbs']))
-    else: print(l)
-PY
+run() { timeout 600 python tools/microbench.py --shapes gateup7b,down7b,gateup70b --formats 8x8x1 --tokens 1 --algos auto --pdl 1 --dequant 0 2>&1 | grep -o "'shape': '[a-z0-9]*'\|'us': [0-9.]*" | paste - - ; }
+echo "== new builder"; run
+cp vllm_pq_b200/libpq_b200.so /tmp/new.so; cp gpurun_out_old_libpq_b200.so vllm_pq_b200/libpq_b200.so
+echo "== old builder"; run
+cp /tmp/new.so vllm_pq_b200/libpq_b200.so
+echo "== new builder again"; run
