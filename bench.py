@@ -155,10 +155,14 @@ def run_reference_arm(args):
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
-        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": args.dtype,
-        "data": "synthetic",
-        "config": {"workload": "llama-2-7b all PQ linears, decode", "batch": args.batch,
-                   "format": args.format, "layers": layers},
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f16" if dtype == torch.float16 else "bf16", "data": "synthetic",
+        # the same workload description as the GPU arm prints (run_gpu_arm); the CPU arm has no
+        # launch / all-reduce modes, and its L2 note does not apply
+        "config": {"workload": f"{args.model} all PQ linears ({layers} layers x qkv,o,gate_up,down), decode",
+                   "batch": args.batch, "format": f"{fmt[0]}bit x d{fmt[1]} x M{fmt[2]}",
+                   "parallelism": f"tp{args.gpus}", "cold_l2": "n/a (host cores)", "launch": "n/a (host cores)",
+                   "allreduce": "none"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
