@@ -36,6 +36,8 @@ SHAPES = {
     "down8b": ([4096], 14336),
     "gateup70b": ([28672] * 2, 8192),
     "down70b": ([8192], 28672),
+    "down7b_tp4": ([4096], 2752),      # row-parallel shards: code pitch 344 / 172 bytes (not a multiple of 16)
+    "down7b_tp8": ([4096], 1376),
 }
 
 

@@ -43,7 +43,9 @@ namespace pq {
 
 constexpr int kL2ConsWarps = 16;                    // four warps per scheduler: the lookups are latency-bound
 constexpr int kL2Cons = kL2ConsWarps * 32;          // consumer threads = rows per iteration
-constexpr int kL2Threads = kL2Cons + 32;            // + one producer warp (a TMA issue costs ~70 cycles)
+constexpr int kL2ProdWarps = 4;                     // warp 16 issues the TMA (~70 cycles per issue); all four copy
+                                                    // when the code pitch rules TMA out.  Registers are allocated
+                                                    // for 20 warps anyway (17 warps get the same 96 per thread).
 constexpr int kL2Tile = 64;                         // positions per table = code bytes per row per box
 constexpr int kL2BoxRows = 64;
 constexpr int kL2BoxBytes = kL2BoxRows * kL2Tile;   // 4 KiB
@@ -277,8 +279,13 @@ __device__ __forceinline__ void l2_lookup16(float (&acc)[4], uint32_t lut_base, 
 }
 
 // MASK: nbits < 8 - codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits).
-template <typename T, int D, bool MASK>
-__global__ void __launch_bounds__(kL2Threads, 1)
+// COPY: the code pitch is not a multiple of 16 bytes - four producer warps copy with cp.async instead
+// of one issuing TMA.  A separate instantiation on purpose: the lookup loop sits at the edge of its
+// 96-register budget, and any extra live value in the kernel makes ptxas rematerialise the column
+// constants inside it (measured: 10 % slower on the large layers, profiles/r1_28).
+template <int COPY> constexpr int l2_threads() { return kL2Cons + 32 * (COPY ? kL2ProdWarps : 1); }
+template <typename T, int D, bool MASK, bool COPY>
+__global__ void __launch_bounds__(l2_threads<COPY>(), 1)
 pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
   extern __shared__ __align__(1024) unsigned char l2_smem_raw[];
   float* lut = reinterpret_cast<float*>(l2_smem_raw);
@@ -329,7 +336,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
 
   if (tid == 0) {
     for (int i = 0; i < a.stages; ++i) {
-      l2_mbar_init(full0 + 8 * i, a.copy_w ? 32 : 1);
+      l2_mbar_init(full0 + 8 * i, COPY ? 32 * kL2ProdWarps : 1);
       l2_mbar_init(empty0 + 8 * i, kL2ConsWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -337,11 +344,11 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   __syncthreads();
   l2_trace(a, 8);
 
-  if (warp == kL2ConsWarps) {
+  if (warp >= kL2ConsWarps) {
     // ================= producer warp: the whole code stream of this CTA, weights only ===========
     pdl_launch_dependents();
-    if (a.copy_w) {
-      // ---- code pitch not a multiple of 16 bytes: no TMA.  All 32 lanes copy the item's
+    if constexpr (COPY) {
+      // ---- code pitch not a multiple of 16 bytes: no TMA.  All 128 producer threads copy the item's
       // [512 rows][64 B] with cp.async (8 or 4 bytes; consecutive lanes = consecutive bytes of a row)
       // and arrive on the stage's barrier when their copies land.  Bytes beyond the row / the
       // matrix are not copied: their table columns are all zero (x is zero beyond K) and rows
@@ -356,7 +363,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         const int nrow = min(kL2Cons, rows - it * kL2Cons);
         const unsigned char* src = a.codes + (size_t)(rb.row0 + it * kL2Cons) * a.Gp + col0;
         const uint32_t dst = ring_addr + stage * kL2StageBytes;
-        for (int idx = lane; idx < nrow * per_row; idx += 32) {
+        for (int idx = tid - kL2Cons; idx < nrow * per_row; idx += 32 * kL2ProdWarps) {
           const int r = idx / per_row, c = (idx - r * per_row) * w;
           if (col0 + c + w <= a.Gp) {
             if (w == 8)
@@ -542,7 +549,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     __syncthreads();
   }
   l2_trace(a, 6);
-  for (int i = fin0 + tid; i < fin1; i += kL2Threads) {
+  for (int i = fin0 + tid; i < fin1; i += l2_threads<COPY>()) {
     const int row = rb.row0 + i;
     float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
     float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
@@ -572,7 +579,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     __syncthreads();
     if (*last_flag) {
       __threadfence();
-      for (int i = fin0 + tid; i < fin1; i += kL2Threads) {
+      for (int i = fin0 + tid; i < fin1; i += l2_threads<COPY>()) {
         const int row = rb.row0 + i;
         float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
         float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
@@ -615,10 +622,10 @@ static int lut2_cluster_slots(int cs, int smem) {
   if (have_dev && cache[dev][l2][sb] > 0) return cache[dev][l2][sb];
   int n = -1;
   if (have_dev) {
-    auto kern = pq_gemv_lut2_kernel<__half, 8, false>;
+    auto kern = pq_gemv_lut2_kernel<__half, 8, false, false>;
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) == cudaSuccess) {
       cudaLaunchConfig_t cfg{};
-      cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(kL2Threads); cfg.dynamicSmemBytes = (sb + 1) * 4096;
+      cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(l2_threads<false>()); cfg.dynamicSmemBytes = (sb + 1) * 4096;
       cudaLaunchAttribute attr[1];
       attr[0].id = cudaLaunchAttributeClusterDimension;
       attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
@@ -760,9 +767,9 @@ static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-template <typename T, int D, bool MASK>
-static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  auto kern = pq_gemv_lut2_kernel<T, D, MASK>;
+template <typename T, int D, bool MASK, bool COPY>
+static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
+  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY>;
   static bool attr_set[64] = {};                   // per instantiation, per device
   int dev = 0;
   cudaGetDevice(&dev);
@@ -773,7 +780,7 @@ static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, 
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.kg * pl.cs, a.T, 1);
-  cfg.blockDim = dim3(kL2Threads);
+  cfg.blockDim = dim3(l2_threads<COPY>());
   cfg.dynamicSmemBytes = pl.smem_total;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -785,6 +792,12 @@ static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, 
   g_lut_last_grid[0] = cfg.gridDim.x; g_lut_last_grid[1] = cfg.gridDim.y;
   g_lut_last_grid[2] = pl.cs; g_lut_last_grid[3] = pl.smem_total;
   return (int)cudaLaunchKernelEx(&cfg, kern, map, a);
+}
+
+template <typename T, int D, bool MASK>
+static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
+  return a.copy_w ? launch_lut2_c<T, D, MASK, true>(map, a, pl, stream)
+                  : launch_lut2_c<T, D, MASK, false>(map, a, pl, stream);
 }
 
 template <typename T>
