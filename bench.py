@@ -223,7 +223,7 @@ def run_gpu_arm(args):
     shape = S.SHAPES[args.model]
     cfg = P.PQConfig(d, b, m, 1)
     with torch.device(device):
-        model = S.PQLlamaLinearStack(shape, cfg, dtype).init_synthetic(seed=rank)
+        model = S.PQLlamaLinearStack(shape, cfg, dtype, fused_act=bool(args.fused_act)).init_synthetic(seed=rank)
     B = args.batch
     stream = torch.cuda.Stream()
 
@@ -308,7 +308,9 @@ def run_gpu_arm(args):
                        "cold_l2": f"each step streams {model.code_bytes() * world / 1e6:.0f} MB of distinct codes (> 126 MB L2)",
                        "launch": ("CUDA graph" if use_graph else "eager") + (" + programmatic dependent launch" if args.pdl else ""),
                        "allreduce": ("one-shot NVLink P2P kernel" if (world > 1 and P.distributed.oneshot_enabled())
-                                     else ("nccl" if world > 1 else "none"))},
+                                     else ("nccl" if world > 1 else "none")),
+                       "mlp_act": ("SiLU(gate)*up on down_proj's x load" if args.fused_act
+                                   else "stand-in slice of gate_up (no activation math)")},
             "e2e": {"value": B / (ms_e2e * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": x_host.numel() * x_host.element_size(),
                     "d2h_bytes_per_step": y_host.numel() * y_host.element_size()},
@@ -346,6 +348,8 @@ def main():
     ap.add_argument("--model", default="llama-2-7b")
     ap.add_argument("--pdl", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--fused-act", type=int, default=0,
+                    help="1: down_proj takes SiLU(gate)*up on its x load (SURVEY 8f N2) instead of the slicing stand-in")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -110,6 +110,25 @@ PQ_API int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, cons
                  const int64_t* part_sizes, int n_parts, int dtype, int algo,
                  void* workspace, int64_t workspace_bytes, void* stream);
 
+/* y = pq_linear(SiLU(x[:, :k]) * x[:, k:]): x is [t, 2k] (gate | up, row stride x_stride >= 2k),
+ * everything else as pq_b200_gemm.  Replaces silu_and_mul + aqlm_gemm of the MLP's down_proj
+ * (vllm/model_executor/models/llama.py:89-93, layers/activation.py:65-84,
+ * csrc/activation_kernels.cu): PQ_ALGO_GEMV_LUT_TMA applies the activation while it loads x;
+ * the other kernels get it from one pq_b200_silu_and_mul launch into the workspace, which must
+ * then hold pq_b200_gemm_silu_mul_workspace_bytes().  Rounding follows the reference kernel:
+ * SiLU in fp32 rounded to the dtype, product rounded to the dtype. */
+PQ_API int pq_b200_gemm_silu_mul(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                          const void* scales, const void* bias, void* y, int64_t y_stride,
+                          int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                          const int64_t* part_sizes, int n_parts, int dtype, int algo,
+                          void* workspace, int64_t workspace_bytes, void* stream);
+PQ_API int64_t pq_b200_gemm_silu_mul_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d,
+                                                     int nbits, int m, int n_parts);
+/* out[t, k] = SiLU(x[:, :k]) * x[:, k:]  <- silu_and_mul  csrc/activation_kernels.cu,
+ * csrc/torch_bindings.cpp (silu_and_mul).  k even; 16-byte loads when k, strides and pointers allow. */
+PQ_API int pq_b200_silu_and_mul(const void* x, int64_t x_stride, void* out, int64_t out_stride, int64_t t,
+                                int64_t k, int dtype, void* stream);
+
 /* 1 if kernel family `algo` covers this problem, else 0 (PQ_ALGO_AUTO: always 1). */
 PQ_API int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 

@@ -189,6 +189,15 @@ def linear_fp32(x: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor,
     return y
 
 
+def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
+    """SiluAndMul.forward_native (vllm/model_executor/layers/activation.py:73-76): the CPU path of
+    the MLP's act_fn (llama.py:89-93).  The CUDA kernel (csrc/activation_kernels.cu:35-38) rounds
+    the same way - SiLU in fp32 rounded to the dtype, then the product rounded to the dtype - so the
+    two agree to the last bit except where expf differs by an ulp across a rounding boundary."""
+    d = x.shape[-1] // 2
+    return F.silu(x[..., :d]) * x[..., d:]
+
+
 def error_report(y: torch.Tensor, y_ref64: torch.Tensor) -> dict:
     """max-abs, max-abs relative to the largest reference output, rms-relative."""
     diff = (y.double() - y_ref64).abs()

@@ -1,5 +1,3 @@
 set -x
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -3
-timeout 600 python bench.py > gpurun_out/r1_30_bench.json 2> gpurun_out/r1_30_bench.err; echo "bench rc=$?"; cat gpurun_out/r1_30_bench.json
+timeout 900 python -m pytest tests/test_gpu_act.py -x -q 2>&1 | tail -15

@@ -29,6 +29,9 @@ _LIBRARY.define("gemm(Tensor input, Tensor codes, Tensor codebooks, Tensor scale
                 "int[] codebook_partition_sizes, Tensor? bias) -> Tensor")
 _LIBRARY.define("gemm_algo(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes, Tensor? bias, int algo) -> Tensor")
+_LIBRARY.define("gemm_silu_mul(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
+                "int[] codebook_partition_sizes, Tensor? bias, int algo) -> Tensor")
+_LIBRARY.define("silu_and_mul(Tensor input) -> Tensor")
 _LIBRARY.define("dequant(Tensor codes, Tensor codebooks, int[] codebook_partition_sizes) -> Tensor")
 _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes) -> Tensor")
@@ -99,13 +102,15 @@ def _dequant_impl(codes, codebooks, scales, parts):
     return out
 
 
-def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo):
+def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo, silu_mul=False):
     _require_cuda(input)
     lib = _lib.load()
     parts, n, g, m, d, nbits = _format(codes, codebooks, parts)
     k = g * d
-    if input.shape[-1] != k:
-        raise RuntimeError(f"PQ: input has {input.shape[-1]} features, weight has {k}")
+    kx = 2 * k if silu_mul else k              # silu_mul: input is (gate | up), llama.py:89-93
+    if input.shape[-1] != kx:
+        raise RuntimeError(f"PQ: input has {input.shape[-1]} features, weight has {k}"
+                           + (" (expects gate|up, twice that)" if silu_mul else ""))
     dt = input.dtype
     if dt not in _DTYPES or codebooks.dtype != dt or scales.dtype != dt:
         raise RuntimeError("PQ: input, codebooks and scales must share one of fp16/bf16")
@@ -113,7 +118,7 @@ def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo):
         raise RuntimeError("PQ: scales must be contiguous [N,1,1,1]")
     if bias is not None and (bias.dtype != dt or bias.numel() != n or not bias.is_contiguous()):
         raise RuntimeError("PQ: bias must be contiguous [N] of the input dtype")
-    x = input.reshape(-1, k)
+    x = input.reshape(-1, kx)
     if x.stride(-1) != 1 or (x.stride(0) * 2) % 16 or x.data_ptr() % 16:
         x = x.contiguous()
     t = x.shape[0]
@@ -124,12 +129,14 @@ def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo):
     with torch.cuda.device(input.device):
         if algo == _lib.ALGO_AUTO:
             algo = lib.pq_b200_pick_algo(t, n, k, d, nbits, m)
-        ws_bytes = lib.pq_b200_workspace_bytes(algo, t, n, k, d, nbits, m, np_)
+        ws_fn = lib.pq_b200_gemm_silu_mul_workspace_bytes if silu_mul else lib.pq_b200_workspace_bytes
+        ws_bytes = ws_fn(algo, t, n, k, d, nbits, m, np_)
         ws = _workspace(input.device, ws_bytes) if ws_bytes else None
-        rc = lib.pq_b200_gemm(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
-                              scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
-                              arr, np_, _DTYPES[dt], algo, _ptr(ws), ws_bytes,
-                              torch.cuda.current_stream().cuda_stream)
+        fn = lib.pq_b200_gemm_silu_mul if silu_mul else lib.pq_b200_gemm
+        rc = fn(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
+                scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
+                arr, np_, _DTYPES[dt], algo, _ptr(ws), ws_bytes,
+                torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "pq::gemm")
     return out.reshape(input.shape[:-1] + (n,))
 
@@ -142,6 +149,27 @@ def _gemm_algo_cuda(input, codes, codebooks, scales, codebook_partition_sizes, b
     return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo)
 
 
+def _gemm_silu_mul_cuda(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo):
+    return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo, silu_mul=True)
+
+
+def _silu_and_mul_cuda(input):
+    _require_cuda(input)
+    if input.dtype not in _DTYPES or input.shape[-1] % 4:
+        raise RuntimeError("PQ: silu_and_mul takes fp16/bf16 [..., 2k] with k even")
+    k = input.shape[-1] // 2
+    x = input.reshape(-1, 2 * k)
+    if x.stride(-1) != 1 or x.stride(0) % 2 or x.data_ptr() % 4:
+        x = x.contiguous()
+    out = torch.empty((x.shape[0], k), dtype=input.dtype, device=input.device)
+    if x.shape[0]:
+        with torch.cuda.device(input.device):
+            rc = _lib.load().pq_b200_silu_and_mul(x.data_ptr(), x.stride(0), out.data_ptr(), k, x.shape[0], k,
+                                                  _DTYPES[input.dtype], torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "pq::silu_and_mul")
+    return out.reshape(input.shape[:-1] + (k,))
+
+
 def _dequant_cuda(codes, codebooks, codebook_partition_sizes):
     return _dequant_impl(codes, codebooks, None, codebook_partition_sizes)
 
@@ -152,6 +180,8 @@ def _dequant_scaled_cuda(codes, codebooks, scales, codebook_partition_sizes):
 
 _LIBRARY.impl("gemm", _gemm_cuda, "CUDA")
 _LIBRARY.impl("gemm_algo", _gemm_algo_cuda, "CUDA")
+_LIBRARY.impl("gemm_silu_mul", _gemm_silu_mul_cuda, "CUDA")
+_LIBRARY.impl("silu_and_mul", _silu_and_mul_cuda, "CUDA")
 _LIBRARY.impl("dequant", _dequant_cuda, "CUDA")
 _LIBRARY.impl("dequant_scaled", _dequant_scaled_cuda, "CUDA")
 
@@ -184,6 +214,9 @@ def _dequant_scaled_fake(codes, codebooks, scales, codebook_partition_sizes):
 
 torch.library.register_fake("pq::gemm")(_gemm_fake)
 torch.library.register_fake("pq::gemm_algo")(_gemm_algo_fake)
+torch.library.register_fake("pq::gemm_silu_mul")(_gemm_algo_fake)
+torch.library.register_fake("pq::silu_and_mul")(
+    lambda input: torch.empty(input.shape[:-1] + (input.shape[-1] // 2,), dtype=input.dtype, device=input.device))
 torch.library.register_fake("pq::dequant")(_dequant_fake)
 torch.library.register_fake("pq::dequant_scaled")(_dequant_scaled_fake)
 
@@ -195,6 +228,19 @@ def pq_gemm(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor,
     if algo == _lib.ALGO_AUTO:
         return torch.ops.pq.gemm(input, codes, codebooks, scales, codebook_partition_sizes, bias)
     return torch.ops.pq.gemm_algo(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo)
+
+
+def pq_gemm_silu_mul(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor,
+                     scales: torch.Tensor, codebook_partition_sizes: List[int],
+                     bias: Optional[torch.Tensor], algo: int = _lib.ALGO_AUTO) -> torch.Tensor:
+    """pq_gemm(SiLU(input[..., :k]) * input[..., k:], ...): the MLP's act_fn + down_proj
+    (llama.py:89-93) in one call; the decode table GEMV applies the activation on its x load."""
+    return torch.ops.pq.gemm_silu_mul(input, codes, codebooks, scales, codebook_partition_sizes, bias, algo)
+
+
+def silu_and_mul(input: torch.Tensor) -> torch.Tensor:
+    """SiluAndMul.forward_cuda (layers/activation.py:65-84) on this library's kernel."""
+    return torch.ops.pq.silu_and_mul(input)
 
 
 def pq_dequant(codes: torch.Tensor, codebooks: torch.Tensor,

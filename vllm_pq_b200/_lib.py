@@ -38,6 +38,12 @@ SIGNATURES = {
     "pq_b200_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
                              c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "pq_b200_gemm_silu_mul": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
+                                      c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "pq_b200_gemm_silu_mul_workspace_bytes": (c_int64, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int,
+                                                        c_int]),
+    "pq_b200_silu_and_mul": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p]),
     "pq_b200_algo_supported": (c_int, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_pick_algo": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_allreduce_oneshot": (c_int, [c_void_p, c_void_p, c_int64, c_int, _VPP, _VPP, c_int, c_int,

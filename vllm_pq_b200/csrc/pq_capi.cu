@@ -18,7 +18,8 @@ bool gemv_lut_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m
 bool gemv_lut_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemv_lut2_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
                        void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
-                       int, int, void*, int64_t, cudaStream_t);
+                       int, int, void*, int64_t, cudaStream_t, int xact);
+int silu_and_mul_dispatch(const void*, int64_t, void*, int64_t, int64_t, int64_t, int, cudaStream_t);
 int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 bool gemv_lut2_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
@@ -142,26 +143,53 @@ int64_t pq_b200_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d
   return 0;
 }
 
-int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
-                 const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
-                 int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
-                 int n_parts, int dtype, int algo, void* workspace, int64_t workspace_bytes,
-                 void* stream) {
+}  // extern "C"
+
+// xact = 1: x is [t, 2k] (gate | up) and the layer's input is SiLU(gate) * up.  The TMA table GEMV
+// takes the activation on its x load; every other kernel gets it from a silu_and_mul launch into
+// the head of the workspace.
+static int64_t act_scratch_bytes(int64_t t, int64_t k) { return (t * k * 2 + 255) / 256 * 256; }
+// Offset of the activations in the workspace: behind the kernel's own part and never inside the
+// first 64 KiB, which hold the split-K tickets that every launch leaves at zero for the next
+// one - a caller may hand the same buffer to every call.
+static int64_t act_offset(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts) {
+  const int64_t own = (pq_b200_workspace_bytes(algo, t, n, k, d, nbits, m, n_parts) + 255) / 256 * 256;
+  return own > (64 << 10) ? own : (64 << 10);
+}
+
+static int gemm_impl(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                     const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                     int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                     int n_parts, int dtype, int algo, void* workspace, int64_t workspace_bytes,
+                     void* stream, int xact) {
   int rc = check_format(n, k, d, nbits, m, part_sizes, n_parts, dtype);
   if (rc) return rc;
   if (!x || !codes || !codebooks || !scales || !y) return PQ_ERR_NULL;
-  if (t <= 0 || t > INT32_MAX || x_stride < k || y_stride < n) return PQ_ERR_SHAPE;
+  if (t <= 0 || t > INT32_MAX || x_stride < (xact ? 2 * k : k) || y_stride < n) return PQ_ERR_SHAPE;
   if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
   const bool was_auto = algo == PQ_ALGO_AUTO;
   if (was_auto) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
   cudaStream_t s = (cudaStream_t)stream;
+  if (xact && !(algo == PQ_ALGO_GEMV_LUT_TMA && pq::gemv_lut2_supported(t, n, k, d, nbits, m))) {
+    const int64_t own = act_offset(algo, t, n, k, d, nbits, m, n_parts);
+    if (!workspace || workspace_bytes < own + act_scratch_bytes(t, k) || ((uintptr_t)workspace & 15))
+      return PQ_ERR_WORKSPACE;
+    void* act = (char*)workspace + own;
+    rc = pq::silu_and_mul_dispatch(x, x_stride, act, k, t, k, dtype, s);
+    if (rc) return rc;
+    return gemm_impl(act, k, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                     part_sizes, n_parts, dtype, algo, workspace, own, stream, 0);
+  }
   if (was_auto && algo == PQ_ALGO_GEMV_LUT_TMA) {
     // the one condition only the dispatcher can see: partition sizes that are not a multiple of
     // the TMA super-row (odd row counts with an odd code pitch) - fall back to the other kernels
     rc = pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
-                                nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+                                nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact);
     if (rc != PQ_ERR_UNSUPPORTED) return rc;
     algo = pick_algo_impl(t, n, k, d, nbits, m, false);
+    if (xact)      // the dispatcher refused (partition sizes): activation as its own launch
+      return gemm_impl(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                       part_sizes, n_parts, dtype, algo, workspace, workspace_bytes, stream, 1);
   }
   switch (algo) {
     case PQ_ALGO_GEMV_DIRECT:
@@ -179,7 +207,7 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
     case PQ_ALGO_GEMV_LUT_TMA:
       if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
-                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
+                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact);
     case PQ_ALGO_GEMM_MMA:
       if (!pq::gemm_mma_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemm_mma_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
@@ -187,6 +215,40 @@ int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void*
     default:
       return PQ_ERR_UNSUPPORTED;
   }
+}
+
+extern "C" {
+
+int pq_b200_gemm(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                 const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                 int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                 int n_parts, int dtype, int algo, void* workspace, int64_t workspace_bytes,
+                 void* stream) {
+  return gemm_impl(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                   part_sizes, n_parts, dtype, algo, workspace, workspace_bytes, stream, 0);
+}
+
+int pq_b200_gemm_silu_mul(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                          const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                          int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                          int n_parts, int dtype, int algo, void* workspace, int64_t workspace_bytes,
+                          void* stream) {
+  return gemm_impl(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                   part_sizes, n_parts, dtype, algo, workspace, workspace_bytes, stream, 1);
+}
+
+int64_t pq_b200_gemm_silu_mul_workspace_bytes(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits,
+                                              int m, int n_parts) {
+  if (algo == PQ_ALGO_AUTO) algo = pq_b200_pick_algo(t, n, k, d, nbits, m);
+  return act_scratch_bytes(t, k) + act_offset(algo, t, n, k, d, nbits, m, n_parts);
+}
+
+int pq_b200_silu_and_mul(const void* x, int64_t x_stride, void* out, int64_t out_stride, int64_t t,
+                         int64_t k, int dtype, void* stream) {
+  if (dtype != PQ_F16 && dtype != PQ_BF16) return PQ_ERR_DTYPE;
+  if (!x || !out) return PQ_ERR_NULL;
+  if (t <= 0 || k <= 0 || x_stride < 2 * k || out_stride < k) return PQ_ERR_SHAPE;
+  return pq::silu_and_mul_dispatch(x, x_stride, out, out_stride, t, k, dtype, (cudaStream_t)stream);
 }
 
 int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems, int dtype,

@@ -113,6 +113,17 @@ __device__ __forceinline__ void st_stream_16(void* p, const uint4& v) {
                :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// SiLU(gate) * up on a pair of packed elements, rounded the way the reference's silu_and_mul is
+// (csrc/activation_kernels.cu: (T)(x / (1 + expf(-x))) in fp32, then the product in T).
+template <typename T>
+__device__ __forceinline__ uint32_t silu_mul_pair(uint32_t gate, uint32_t up) {
+  using T2 = typename Traits<T>::T2;
+  const float2 g = Traits<T>::to_f2(gate);
+  uint32_t s = Traits<T>::pack(g.x / (1.0f + expf(-g.x)), g.y / (1.0f + expf(-g.y)));
+  const T2 r = __hmul2(*reinterpret_cast<const T2*>(&s), *reinterpret_cast<const T2*>(&up));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -76,6 +76,7 @@ struct Lut2Args {
   int smem_cb, smem_x;    // bytes
   int mask;               // nbits < 8: codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits)
   unsigned long long* trace;
+  int xact;               // 1: x is [T, 2K] and the input is SiLU(x[:, :K]) * x[:, K:]
   Parts parts;            // cta_end counts clusters
 };
 
@@ -496,7 +497,11 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       for (int s = 0; s < my_tiles; ++s) {
         const int elem = xoff + s * xstep;
         uint32_t v = 0u;
-        if (xoff >= 0 && elem < a.K) v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
+        if (xoff >= 0 && elem < a.K) {
+          v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
+          // x is [T, 2K] = (gate | up): SiLU(gate) * up on the way in (llama.py:89-93)
+          if (a.xact) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+        }
         xs_mine[s * XW] = v;
       }
     }
@@ -820,7 +825,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
                        const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
                        int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
                        int n_parts, int dtype, void* workspace, int64_t workspace_bytes,
-                       cudaStream_t stream) {
+                       cudaStream_t stream, int xact) {
   if ((uintptr_t)codes % 16 || (uintptr_t)x % 4 || (x_stride * 2) % 4) return PQ_ERR_ALIGN;
   Lut2Plan pl;
   if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts)) return PQ_ERR_UNSUPPORTED;
@@ -845,7 +850,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.prefetch = prefetch;
 
   a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
-  a.trace = g_lut_trace;
+  a.trace = g_lut_trace; a.xact = xact;
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
   if (rc) return rc;
   CUtensorMap map;

@@ -274,15 +274,25 @@ class RowParallelLinear(LinearBase):
             loaded_weight = loaded_weight.narrow(input_dim, self.tp_rank * shard, shard)
         _copy(param.data, loaded_weight)
 
-    def forward(self, input_):
+    def forward(self, input_, input_act: Optional[str] = None):
+        """`input_act="silu_and_mul"`: `input_` is this rank's (gate | up) out of the merged
+        column-parallel layer and the layer's input is SiLU(gate) * up (llama.py:89-93) - taken on
+        the kernel's x load instead of by an activation launch in between."""
+        if input_act not in (None, "silu_and_mul"):
+            raise ValueError(f"unknown input activation {input_act!r}")
         if self.input_is_parallel:
             input_parallel = input_
         else:
+            if input_act is not None:
+                raise ValueError("a fused input activation needs input_is_parallel")
             chunk = divide(input_.shape[-1], self.tp_size)
             input_parallel = input_.narrow(-1, self.tp_rank * chunk, chunk).contiguous()
         # bias enters the sum exactly once (linear.py:1206-1208)
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
-        output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
+        if input_act is None:
+            output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
+        else:
+            output_parallel = self.quant_method.apply_silu_mul(self, input_parallel, bias=bias_)
         if self.reduce_results and self.tp_size > 1:
             output = tensor_model_parallel_all_reduce(output_parallel)
         else:

@@ -156,6 +156,13 @@ class PQLinearMethod(LinearMethodBase):
         return ops.pq_gemm(x, layer.codes, codebooks, layer.scales,
                            list(output_partition_sizes), bias)
 
+    def apply_silu_mul(self, layer: torch.nn.Module, x: torch.Tensor,
+                       bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """apply(SiLU(x[..., :k]) * x[..., k:]): act_fn + down_proj of the MLP (llama.py:89-93)."""
+        codebooks = layer.codebooks
+        return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales,
+                                    list(getattr(codebooks, "output_partition_sizes", [])), bias)
+
     def dequantize(self, layer: torch.nn.Module, scaled: bool = True) -> torch.Tensor:
         """Dense [N, K] weight (aqlm.py:37-74); bit-exact with the reference."""
         codebooks = layer.codebooks

@@ -44,8 +44,9 @@ SHAPES = {s.name: s for s in (LLAMA2_7B, LLAMA3_8B, LLAMA2_70B)}
 class PQDecoderLinears(nn.Module):
     """qkv -> o -> gate_up -> down of one decoder layer."""
 
-    def __init__(self, shape: LlamaShape, cfg: PQConfig, dtype: torch.dtype):
+    def __init__(self, shape: LlamaShape, cfg: PQConfig, dtype: torch.dtype, fused_act: bool = False):
         super().__init__()
+        self.fused_act = fused_act
         kw = dict(bias=False, params_dtype=dtype, quant_config=cfg)
         self.qkv_proj = QKVParallelLinear(shape.hidden, shape.head_dim, shape.heads, shape.kv_heads, **kw)
         self.o_proj = RowParallelLinear(shape.heads * shape.head_dim, shape.hidden, **kw)
@@ -63,6 +64,9 @@ class PQDecoderLinears(nn.Module):
         attn = qkv[..., :self.q_width]                  # stand-in for attention: keeps the dependency
         h, _ = self.o_proj(attn)
         gate_up, _ = self.gate_up_proj(h)
+        if self.fused_act:                              # the real MLP: SiLU(gate) * up on down_proj's x load
+            h, _ = self.down_proj(gate_up, input_act="silu_and_mul")
+            return h
         act = gate_up[..., :self.mlp_width]             # stand-in for SiLU(gate) * up
         h, _ = self.down_proj(act)
         return h
@@ -70,11 +74,11 @@ class PQDecoderLinears(nn.Module):
 
 class PQLlamaLinearStack(nn.Module):
     def __init__(self, shape: LlamaShape, cfg: PQConfig, dtype: torch.dtype = torch.float16,
-                 n_layers: int = None):
+                 n_layers: int = None, fused_act: bool = False):
         super().__init__()
         self.shape, self.cfg, self.dtype = shape, cfg, dtype
         n_layers = shape.layers if n_layers is None else n_layers
-        self.layers = nn.ModuleList(PQDecoderLinears(shape, cfg, dtype) for _ in range(n_layers))
+        self.layers = nn.ModuleList(PQDecoderLinears(shape, cfg, dtype, fused_act) for _ in range(n_layers))
 
     @torch.no_grad()
     def init_synthetic(self, seed: int = 0) -> "PQLlamaLinearStack":
