@@ -152,3 +152,33 @@ def test_tp1_layers_build():
     up = torch.randn(11008, 1, 1, 1).half()
     gu.weight_loader(gu.scales, up, 1)
     assert torch.equal(gu.scales.data[11008:], up)
+
+
+def test_silu_mul_ops_fake_shapes_and_hook_checks():
+    """the fused-activation ops trace like the plain ones (gate|up in, N out), and
+    RowParallelLinear refuses activations it does not know or an input it would have to slice."""
+    x2 = torch.empty(2, 3, 2 * 11008, dtype=torch.float16, device="meta")
+    codes = torch.empty(4096, 1376, 1, dtype=torch.int8, device="meta")
+    cb = torch.empty(1, 256, 1, 8, dtype=torch.float16, device="meta")
+    sc = torch.empty(4096, 1, 1, 1, dtype=torch.float16, device="meta")
+    y = torch.ops.pq.gemm_silu_mul(x2, codes, cb, sc, [4096], None, 0)
+    assert y.shape == (2, 3, 4096) and y.dtype == torch.float16
+    a = torch.ops.pq.silu_and_mul(x2)
+    assert a.shape == (2, 3, 11008) and a.dtype == torch.float16
+    torch.library.opcheck(torch.ops.pq.silu_and_mul.default, (x2,), test_utils=("test_schema",))
+
+    cfg = P.PQConfig(8, 8, 1, 1)
+    down = P.RowParallelLinear(256, 128, bias=False, params_dtype=torch.float16, quant_config=cfg)
+    with pytest.raises(ValueError, match="unknown input activation"):
+        down(torch.zeros(1, 512, dtype=torch.float16), input_act="gelu")
+    sliced = P.RowParallelLinear(256, 128, bias=False, input_is_parallel=False, params_dtype=torch.float16,
+                                 quant_config=cfg)
+    with pytest.raises(ValueError, match="input_is_parallel"):
+        sliced(torch.zeros(1, 512, dtype=torch.float16), input_act="silu_and_mul")
+    # no CPU fallback: the fused call on CPU tensors fails loudly, like the plain one
+    with pytest.raises((RuntimeError, NotImplementedError)):
+        down(torch.zeros(1, 512, dtype=torch.float16), input_act="silu_and_mul")
+    # the oracle's activation is the reference's forward_native (activation.py:73-76)
+    from oracle import pq_oracle as O
+    v = torch.tensor([[1.0, -2.0, 0.5, 3.0]], dtype=torch.float16)
+    assert torch.equal(O.silu_and_mul(v), torch.nn.functional.silu(v[:, :2]) * v[:, 2:])
