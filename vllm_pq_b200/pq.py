@@ -25,6 +25,13 @@ from .plugin_api import (LinearMethodBase, QuantizationConfig, register_quantiza
                          set_weight_attrs)
 
 
+def _from_keys(config: Dict[str, Any], key: str) -> Any:
+    """base_config.py:104-112 (get_from_keys), same error."""
+    if key in config:
+        return config[key]
+    raise ValueError(f"Cannot find any of {[key]} in the model's quantization config.")
+
+
 def get_int_dtype(nbits: int) -> torch.dtype:
     """Storage type of a code (aqlm.py:20-29); a 4-bit code still takes an int8."""
     for limit, dt in ((8, torch.int8), (16, torch.int16), (32, torch.int32), (64, torch.int64)):
@@ -33,13 +40,19 @@ def get_int_dtype(nbits: int) -> torch.dtype:
     raise ValueError(f"No dtype available for {nbits}-bit codebooks")
 
 
-@register_quantization_config("pq")
-class PQConfig(QuantizationConfig):
-    """Config class for PQ (AQLM-format) checkpoints.  aqlm.py:159-217."""
+class PQConfigBody:
+    """Method bodies of the PQ config (aqlm.py:159-217), independent of the ABC they are mounted on:
+    ``make_classes`` combines them with this package's restated ABCs (stand-alone) or with vLLM's own
+    ``QuantizationConfig`` (``vllm_plugin.register``).  No zero-argument ``super()`` in here - its
+    ``__class__`` cell would pin the bodies to one base."""
+
+    _config_base: type = object                              # set by make_classes
+    _method_cls: type = None                                 # "
+    _is_linear = staticmethod(lambda layer: False)           # "
 
     def __init__(self, in_group_size: int, nbits_per_codebook: int, num_codebooks: int,
                  out_group_size: int = 1) -> None:
-        super().__init__()
+        type(self)._config_base.__init__(self)
         self.in_group_size = in_group_size
         self.nbits_per_codebook = nbits_per_codebook
         self.num_codebooks = num_codebooks
@@ -57,7 +70,7 @@ class PQConfig(QuantizationConfig):
 
     @classmethod
     def get_name(cls) -> str:
-        return "pq"
+        return cls._registered_name
 
     @classmethod
     def get_supported_act_dtypes(cls) -> List[torch.dtype]:
@@ -73,29 +86,27 @@ class PQConfig(QuantizationConfig):
 
     @classmethod
     def from_config(cls, config: Dict[str, Any]) -> "PQConfig":
-        return cls(cls.get_from_keys(config, ["in_group_size"]),
-                   cls.get_from_keys(config, ["nbits_per_codebook"]),
-                   cls.get_from_keys(config, ["num_codebooks"]),
-                   cls.get_from_keys(config, ["out_group_size"]))
+        return cls(_from_keys(config, "in_group_size"), _from_keys(config, "nbits_per_codebook"),
+                   _from_keys(config, "num_codebooks"), _from_keys(config, "out_group_size"))
 
     @classmethod
     def override_quantization_method(cls, hf_quant_cfg, user_quant) -> Optional[str]:
         # An AQLM checkpoint can be served by this method when the user asks for it.
-        if user_quant == "pq" and hf_quant_cfg.get("quant_method") in ("aqlm", "pq"):
-            return "pq"
+        name = cls._registered_name
+        if user_quant == name and hf_quant_cfg.get("quant_method") in ("aqlm", name):
+            return name
         return None
 
-    def get_quant_method(self, layer: torch.nn.Module, prefix: str) -> Optional["PQLinearMethod"]:
-        from .linear import is_linear_layer
-        if is_linear_layer(layer):
-            return PQLinearMethod(self)
+    def get_quant_method(self, layer: torch.nn.Module, prefix: str = "") -> Optional["PQLinearMethod"]:
+        if type(self)._is_linear(layer):
+            return type(self)._method_cls(self)
         return None                                          # embeddings / lm_head stay dense
 
 
-class PQLinearMethod(LinearMethodBase):
-    """Linear method for PQ.  aqlm.py:220-374."""
+class PQLinearMethodBody:
+    """Method bodies of the PQ linear method (aqlm.py:220-374); see PQConfigBody."""
 
-    def __init__(self, quant_config: PQConfig):
+    def __init__(self, quant_config: "PQConfig"):
         self.quant_config = quant_config
 
     def create_weights(self, layer: torch.nn.Module, input_size_per_partition: int,
@@ -168,3 +179,26 @@ class PQLinearMethod(LinearMethodBase):
         codebooks = layer.codebooks
         parts = list(getattr(codebooks, "output_partition_sizes", []))
         return ops.pq_dequant(layer.codes, codebooks, parts, layer.scales if scaled else None)
+
+
+def make_classes(config_base: type, method_base: type, is_linear, name: str = "pq"):
+    """(PQConfig, PQLinearMethod) as real subclasses of the given ABCs.  ``is_linear(layer)`` is the
+    ``isinstance(layer, LinearBase)`` test of aqlm.py:213-217 for whichever LinearBase is in use."""
+    method_cls = type("PQLinearMethod", (PQLinearMethodBody, method_base),
+                      {"__doc__": PQLinearMethodBody.__doc__, "__module__": __name__})
+    config_cls = type("PQConfig", (PQConfigBody, config_base), {
+        "__doc__": "Config class for PQ (AQLM-format) checkpoints.  aqlm.py:159-217.",
+        "__module__": __name__,
+        "_config_base": config_base, "_method_cls": method_cls, "_is_linear": staticmethod(is_linear),
+        "_registered_name": name,
+    })
+    return config_cls, method_cls
+
+
+def _is_own_linear(layer) -> bool:
+    from .linear import is_linear_layer
+    return is_linear_layer(layer)
+
+
+PQConfig, PQLinearMethod = make_classes(QuantizationConfig, LinearMethodBase, _is_own_linear)
+PQConfig = register_quantization_config("pq")(PQConfig)

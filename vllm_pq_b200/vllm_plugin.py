@@ -9,8 +9,9 @@ Stand-alone (no vLLM) the package uses its own restatement of the plugin ABCs
 subclasses of vLLM's own ``QuantizationConfig`` / ``LinearMethodBase``
 (``register_quantization_config`` checks ``issubclass``,
 quantization/__init__.py:62-67) and ``get_quant_method`` must recognise vLLM's
-``LinearBase`` (aqlm.py:213-217).  ``register()`` builds those subclasses from
-the same method bodies; nothing else differs.
+``LinearBase`` (aqlm.py:213-217).  ``register()`` asks ``pq.make_classes`` for the same
+method bodies (``PQConfigBody`` / ``PQLinearMethodBody``) mounted on vLLM's bases; nothing else
+differs.  Tested against the vLLM installed in the image: tests/test_vllm_plugin_cpu.py.
 """
 from __future__ import annotations
 
@@ -18,7 +19,8 @@ _REGISTERED = None
 
 
 def register(name: str = "pq"):
-    """Idempotent; returns the registered config class."""
+    """Idempotent; returns the registered config class (a subclass of vLLM's QuantizationConfig whose
+    ``get_quant_method`` hands vLLM's LinearBase layers a subclass of vLLM's LinearMethodBase)."""
     global _REGISTERED
     if _REGISTERED is not None:
         return _REGISTERED
@@ -26,20 +28,9 @@ def register(name: str = "pq"):
     from vllm.model_executor.layers.quantization import register_quantization_config
     from vllm.model_executor.layers.quantization.base_config import QuantizationConfig
 
-    from .pq import PQConfig, PQLinearMethod
+    from .pq import make_classes
 
-    skip = ("__dict__", "__weakref__", "__module__", "__doc__", "__abstractmethods__", "_abc_impl")
-
-    def rebase(cls, base, new_name):
-        body = {k: v for k, v in vars(cls).items() if k not in skip}
-        return type(new_name, (base,), body)
-
-    method_cls = rebase(PQLinearMethod, LinearMethodBase, "PQLinearMethod")
-
-    def get_quant_method(self, layer, prefix):
-        return method_cls(self) if isinstance(layer, LinearBase) else None
-
-    config_cls = rebase(PQConfig, QuantizationConfig, "PQConfig")
-    config_cls.get_quant_method = get_quant_method
+    config_cls, _ = make_classes(QuantizationConfig, LinearMethodBase,
+                                 lambda layer: isinstance(layer, LinearBase), name)
     _REGISTERED = register_quantization_config(name)(config_cls)
     return _REGISTERED
