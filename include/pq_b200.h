@@ -82,6 +82,12 @@ PQ_API void pq_b200_debug_last_launch(int* out4);
  * rows per cluster, grid.x, smem bytes} of the last PQ_ALGO_GEMM_MMA launch. */
 PQ_API void pq_b200_debug_last_mma_plan(int* out8);
 PQ_API int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes);
+/* The table GEMV's launch plan for a problem: {consumer warps per CTA, cluster size, tiles per CTA,
+ * K groups, rows per cluster, ring stages, shared-memory bytes, 64-position tiles, grid.x}. */
+PQ_API int pq_b200_debug_lut_tma_plan(int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                                      const int64_t* part_sizes, int n_parts, int* out9);
+/* cudaOccupancyMaxActiveClusters of the TMA table GEMV's CTA shape (8 or 16 consumer warps). */
+PQ_API int pq_b200_debug_lut_tma_slots(int consumer_warps, int cluster_size, int smem_bytes);
 
 /* Unscaled (scales == NULL; what aqlm_dequant returns, gemm_kernels.cu:563-592) or
  * scaled (aqlm.py:70-72) weights w_out[n, k].  Sum over the m codebooks is
@@ -92,7 +98,9 @@ PQ_API int pq_b200_dequant(const void* codes, const void* codebooks, const void*
                     void* w_out, int64_t n, int64_t k, int d, int nbits, int m,
                     const int64_t* part_sizes, int n_parts, int dtype, void* stream);
 
-/* Workspace (bytes) pq_b200_gemm needs for this problem with `algo`.  The first 64 KiB of a
+/* Workspace (bytes) pq_b200_gemm can use for this problem with `algo`; it is OPTIONAL: given NULL
+ * (or fewer bytes) every kernel still runs - the table GEMV then keeps each row block inside one
+ * cluster instead of splitting K across clusters, which costs long-K layers some speed.  The first 64 KiB of a
  * non-empty workspace hold split-K ticket counters: they must be ZERO before the first call and
  * every call leaves them zero, so one zero-initialised buffer can be reused for all calls that
  * are ordered on a stream (the rest of the workspace is scratch).  256-byte aligned. */

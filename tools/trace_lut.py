@@ -15,7 +15,8 @@ from vllm_pq_b200 import _lib  # noqa: E402
 PHASES = ["start", "prefetch issued", "pdl wait done", "x staged + codebooks", "table 0 built",
           "lookups done", "pushed + cluster barrier", "reduced + y stored", "(lut_tma) barriers ready",
           "(lut_tma) item 0 done", "(lut_tma) warp 0 table stores issued", "(lut_tma) x loads issued",
-          "(lut_tma) codebooks landed"]
+          "(lut_tma) codebooks landed", "(lut_tma) table 1 built", "(lut_tma) tile 1 item 0 done",
+          "(lut_tma) tile 0 items done"]
 
 
 def main():
@@ -26,14 +27,15 @@ def main():
     ap.add_argument("--m", type=int, default=1)
     ap.add_argument("--t", type=int, default=1)
     ap.add_argument("--nsets", type=int, default=12)
-    ap.add_argument("--algo", type=int, default=_lib.ALGO_GEMV_LUT)
+    ap.add_argument("--algo", type=int, default=_lib.ALGO_GEMV_LUT_TMA)
     ap.add_argument("--pdl", type=int, default=0)
+    ap.add_argument("--chain", type=int, default=0, help="launch the traced kernel right after N others (PDL chain)")
     a = ap.parse_args()
     lib = _lib.load()
     P.ops.set_pdl(bool(a.pdl))
-    for smem in (100 * 1024, 110 * 1024, 118 * 1024):
-        print("max active clusters @%d KiB:" % (smem // 1024),
-              {cs: lib.pq_b200_debug_max_active_clusters(cs, smem) for cs in (1, 2, 4, 8)})
+    for cw, smem in ((8, 100 * 1024), (8, 112 * 1024), (16, 200 * 1024)):
+        print("max active clusters, %d consumer warps @%d KiB:" % (cw, smem // 1024),
+              {cs: lib.pq_b200_debug_lut_tma_slots(cw, cs, smem) for cs in (1, 2, 4, 8, 16)})
     parts = [a.n // a.parts] * a.parts
     sets = []
     for _ in range(a.nsets):
@@ -46,6 +48,8 @@ def main():
     for s in sets:          # warm-up (also evicts the first sets from L2)
         P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=a.algo)
     torch.cuda.synchronize()
+    for s in sets[1:1 + a.chain]:
+        P.ops.pq_gemm(x, s[0], s[1], s[2], parts, None, algo=a.algo)
     lib.pq_b200_debug_set_trace(trace.data_ptr())
     P.ops.pq_gemm(x, sets[0][0], sets[0][1], sets[0][2], parts, None, algo=a.algo)
     torch.cuda.synchronize()

@@ -37,20 +37,35 @@ _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes) -> Tensor")
 
 
-# One persistent, zero-initialised workspace per device.  The split-K kernels keep ticket
-# counters in its first 64 KiB and leave them zero (include/pq_b200.h), so it is zeroed only
-# when (re)allocated; reusing it also keeps allocator traffic off the decode path.
+# One zero-initialised workspace per (device, stream).  The split-K kernels keep ticket counters in
+# its first 64 KiB and leave them zero (include/pq_b200.h), so it is zeroed only when allocated.
+#  * per stream: two streams of one device must not share tickets and partial sums;
+#  * never freed: a CUDA graph captured earlier holds the raw pointer, so a buffer that is outgrown
+#    is retired (kept alive), not dropped - replaying the old graph stays valid;
+#  * the SiLU*mul scratch of gemm_silu_mul is NOT in here: it is a per-call torch tensor
+#    (stream-ordered, graph-pool safe), see _gemm_impl.
 _WORKSPACES = {}
+_RETIRED = []
+_WS_MIN_BYTES = 8 << 20
 
 
-def _workspace(device: torch.device, nbytes: int) -> torch.Tensor:
-    ws = _WORKSPACES.get(device)
+def _workspace(device: torch.device, nbytes: int) -> Optional[torch.Tensor]:
+    key = (device.index if device.index is not None else torch.cuda.current_device(),
+           torch.cuda.current_stream(device).cuda_stream)
+    ws = _WORKSPACES.get(key)
     if ws is not None and ws.numel() >= nbytes:
         return ws
-    size = max(int(nbytes) * 2, 32 << 20)
+    if torch.cuda.is_current_stream_capturing():
+        # No buffer of this stream from before the capture (callers warm up eagerly on the capture
+        # stream first, as vLLM does): allocating here would put a memset node in front of every
+        # launch.  The workspace is optional (include/pq_b200.h): without it the table GEMV plans
+        # without K groups.
+        return None
+    size = max(int(nbytes) * 2, _WS_MIN_BYTES)
     new = torch.zeros(size, dtype=torch.uint8, device=device)
-    if not torch.cuda.is_current_stream_capturing():
-        _WORKSPACES[device] = new        # a buffer born inside a graph capture lives in the graph's pool
+    if ws is not None:
+        _RETIRED.append(ws)
+    _WORKSPACES[key] = new
     return new
 
 
@@ -129,13 +144,19 @@ def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo, silu_mul=Fals
     with torch.cuda.device(input.device):
         if algo == _lib.ALGO_AUTO:
             algo = lib.pq_b200_pick_algo(t, n, k, d, nbits, m)
-        ws_fn = lib.pq_b200_gemm_silu_mul_workspace_bytes if silu_mul else lib.pq_b200_workspace_bytes
-        ws_bytes = ws_fn(algo, t, n, k, d, nbits, m, np_)
+        if silu_mul and not (algo == _lib.ALGO_GEMV_LUT_TMA and
+                             lib.pq_b200_algo_supported(algo, t, n, k, d, nbits, m)):
+            # no kernel of this family takes the activation on its x load: one silu_and_mul launch
+            # into a per-call tensor, then the plain linear (bit-identical to the C entry point's
+            # own two-launch form, tests/test_gpu_act.py)
+            act = _silu_and_mul_cuda(x)
+            return _gemm_impl(act, codes, codebooks, scales, parts, bias, algo).reshape(input.shape[:-1] + (n,))
+        ws_bytes = lib.pq_b200_workspace_bytes(algo, t, n, k, d, nbits, m, np_)
         ws = _workspace(input.device, ws_bytes) if ws_bytes else None
         fn = lib.pq_b200_gemm_silu_mul if silu_mul else lib.pq_b200_gemm
         rc = fn(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
                 scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
-                arr, np_, _DTYPES[dt], algo, _ptr(ws), ws_bytes,
+                arr, np_, _DTYPES[dt], algo, _ptr(ws), ws.numel() if ws is not None else 0,
                 torch.cuda.current_stream().cuda_stream)
     _lib.check(rc, "pq::gemm")
     return out.reshape(input.shape[:-1] + (n,))

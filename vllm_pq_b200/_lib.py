@@ -32,6 +32,9 @@ SIGNATURES = {
     "pq_b200_debug_last_launch": (None, [ctypes.POINTER(c_int)]),
     "pq_b200_debug_last_mma_plan": (None, [ctypes.POINTER(c_int)]),
     "pq_b200_debug_max_active_clusters": (c_int, [c_int, c_int]),
+    "pq_b200_debug_lut_tma_slots": (c_int, [c_int, c_int, c_int]),
+    "pq_b200_debug_lut_tma_plan": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
+                                           ctypes.POINTER(c_int)]),
     "pq_b200_dequant": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int,
                                 c_int, c_int, _I64P, c_int, c_int, c_void_p]),
     "pq_b200_workspace_bytes": (c_int64, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int]),

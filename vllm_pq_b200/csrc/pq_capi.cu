@@ -39,6 +39,8 @@ extern unsigned long long* g_lut_trace;
 extern int g_lut_last_grid[4];
 extern int g_mm_last_plan[8];
 int lut_max_active_clusters(int cs, int smem);
+int gemv_lut2_debug_plan(int64_t, int64_t, int64_t, int, int, int, const int64_t*, int, int*);
+int gemv_lut2_debug_slots(int cw, int cs, int smem);
 }  // namespace pq
 
 static int check_format(int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
@@ -80,6 +82,13 @@ void pq_b200_set_pdl(int enabled) { pq::g_use_pdl = enabled != 0; }
 void pq_b200_debug_set_trace(void* device_buffer) { pq::g_lut_trace = (unsigned long long*)device_buffer; }
 void pq_b200_debug_last_launch(int* out4) { for (int i = 0; i < 4; ++i) out4[i] = pq::g_lut_last_grid[i]; }
 void pq_b200_debug_last_mma_plan(int* out8) { for (int i = 0; i < 8; ++i) out8[i] = pq::g_mm_last_plan[i]; }
+int pq_b200_debug_lut_tma_plan(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                               int n_parts, int* out9) {
+  return pq::gemv_lut2_debug_plan(t, n, k, d, nbits, m, part_sizes, n_parts, out9);
+}
+int pq_b200_debug_lut_tma_slots(int consumer_warps, int cluster_size, int smem_bytes) {
+  return pq::gemv_lut2_debug_slots(consumer_warps, cluster_size, smem_bytes);
+}
 int pq_b200_debug_max_active_clusters(int cluster_size, int smem_bytes) {
   return pq::lut_max_active_clusters(cluster_size, smem_bytes);
 }

@@ -41,18 +41,21 @@
 
 namespace pq {
 
-constexpr int kL2ConsWarps = 16;                    // four warps per scheduler: the lookups are latency-bound
-constexpr int kL2Cons = kL2ConsWarps * 32;          // consumer threads = rows per iteration
-constexpr int kL2ProdWarps = 4;                     // warp 16 issues the TMA (~70 cycles per issue); all four copy
-                                                    // when the code pitch rules TMA out.  Registers are allocated
-                                                    // for 20 warps anyway (17 warps get the same 96 per thread).
+// Two CTA shapes (template parameter CW = consumer warps; one lane owns one row, so a row
+// iteration covers CW * 32 rows):
+//   CW = 16: one CTA per SM, 96 registers, 140-215 KB of shared memory - the throughput shape
+//            (four warps per scheduler: the lookups are latency-bound);
+//   CW = 8:  at most 112 registers and 113 KB, so TWO CTAs fit one SM: under programmatic
+//            dependent launch the next layer's CTA is co-resident and runs its whole prologue
+//            (codebooks, barriers, the first code stages, lane constants) while this layer
+//            computes - the latency shape for the Llama-2-7B sized layers.
+constexpr int kL2ProdWarps = 4;                     // the first issues the TMA (~70 cycles per issue); all four copy
+                                                    // when the code pitch rules TMA out (COPY instantiation)
 constexpr int kL2Tile = 64;                         // positions per table = code bytes per row per box
 constexpr int kL2BoxRows = 64;
 constexpr int kL2BoxBytes = kL2BoxRows * kL2Tile;   // 4 KiB
-constexpr int kL2StageBoxes = kL2Cons / kL2BoxRows; // 8
-constexpr int kL2StageBytes = kL2Cons * kL2Tile;    // 32 KiB = 8 boxes
-constexpr int kL2MaxStages = 4;
-constexpr int kL2MaxCluster = 8;
+constexpr int kL2MaxStages = 6;
+constexpr int kL2MaxCluster = 16;                   // 16 needs cudaFuncAttributeNonPortableClusterSizeAllowed
 constexpr int kL2MaxT = 8;
 
 struct Lut2Args {
@@ -77,12 +80,14 @@ struct Lut2Args {
   int mask;               // nbits < 8: codes are masked to nbits (aqlm.py:29-34 takes them mod 2^nbits)
   unsigned long long* trace;
   int xact;               // 1: x is [T, 2K] and the input is SiLU(x[:, :K]) * x[:, K:]
+  int early_ld;           // griddepcontrol.launch_dependents at kernel entry (experiment knob)
+  int trace_mask;         // which trace slots stamp (a %globaltimer read is slow: few stamps perturb less)
   Parts parts;            // cta_end counts clusters
 };
 
 constexpr int kL2TraceSlots = 16;
 __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
-  if (a.trace != nullptr && threadIdx.x == 0) {
+  if (a.trace != nullptr && threadIdx.x == 0 && ((a.trace_mask >> slot) & 1)) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
@@ -92,7 +97,7 @@ __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
 // BAR.SYNC does not block at issue: a stamp right after a barrier shows when this warp ARRIVED.
 // This one waits for `dep` (a value read after the barrier from another warp's data) first.
 __device__ __forceinline__ void l2_trace_dep(const Lut2Args& a, int slot, const volatile uint32_t* p) {
-  if (a.trace != nullptr && threadIdx.x == 0) {
+  if (a.trace != nullptr && threadIdx.x == 0 && ((a.trace_mask >> slot) & 1)) {
     const uint32_t dep = *p;
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
@@ -133,8 +138,8 @@ __device__ __forceinline__ void l2_tma_prefetch(const CUtensorMap* map, int c0, 
 __device__ __forceinline__ void l2_cp_async_16(uint32_t dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ void l2_cons_sync() {      // the 8 consumer warps only
-  asm volatile("bar.sync 1, %0;" :: "n"(kL2Cons) : "memory");
+template <int CONS> __device__ __forceinline__ void l2_cons_sync() {      // the consumer warps only
+  asm volatile("bar.sync 1, %0;" :: "n"(CONS) : "memory");
 }
 __device__ __forceinline__ uint32_t l2_cluster_rank() {
   uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;
@@ -195,7 +200,7 @@ __device__ __forceinline__ int l2_x_offset(int f, int tile, int M) {
 // (c = tq, j = hb) and of word (c = tq, j = hb + 2): columns 32 hb + 4 tq + {0..3} and
 // 32 hb + 16 + 4 tq + {0..3} - two 128-bit stores per entry row; odd g stores them in the other
 // order so that the 8 lanes of a store phase cover all 32 banks.
-template <typename T, int D, int M>
+template <typename T, int D, int M, int CW>
 __device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* xt, int E, int hb,
                                               int warp, int lane) {
   const int g = lane >> 2, tq = lane & 3;
@@ -210,7 +215,7 @@ __device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* 
     b0[jn] = x32[(hb * 4 + jn) * 32 + lane];
     b1[jn] = D == 16 ? x32[256 + (hb * 4 + jn) * 32 + lane] : 0u;
   }
-  for (int eb = warp; eb * 16 < E; eb += kL2ConsWarps) {
+  for (int eb = warp; eb * 16 < E; eb += CW) {
     const int e0 = eb * 16 + g, e1 = e0 + 8;
     uint32_t fa[M][4];
 #pragma unroll
@@ -250,14 +255,14 @@ __device__ __forceinline__ void l2_build_half(float* lut, const T* cb, const T* 
   }
 }
 
-template <typename T, int D>
+template <typename T, int D, int CW>
 __device__ __forceinline__ void l2_build_table(float* lut, const T* cb, const T* xt, int E, int M,
                                                int warp, int lane) {
 #pragma unroll
   for (int hb = 0; hb < 2; ++hb) {
-    if (M == 1) l2_build_half<T, D, 1>(lut, cb, xt, E, hb, warp, lane);
-    else if (M == 2) l2_build_half<T, D, 2>(lut, cb, xt, E, hb, warp, lane);
-    else l2_build_half<T, D, 4>(lut, cb, xt, E, hb, warp, lane);
+    if (M == 1) l2_build_half<T, D, 1, CW>(lut, cb, xt, E, hb, warp, lane);
+    else if (M == 2) l2_build_half<T, D, 2, CW>(lut, cb, xt, E, hb, warp, lane);
+    else l2_build_half<T, D, 4, CW>(lut, cb, xt, E, hb, warp, lane);
   }
 }
 
@@ -284,10 +289,14 @@ __device__ __forceinline__ void l2_lookup16(float (&acc)[4], uint32_t lut_base, 
 // of one issuing TMA.  A separate instantiation on purpose: the lookup loop sits at the edge of its
 // 96-register budget, and any extra live value in the kernel makes ptxas rematerialise the column
 // constants inside it (measured: 10 % slower on the large layers, profiles/r1_28).
-template <int COPY> constexpr int l2_threads() { return kL2Cons + 32 * (COPY ? kL2ProdWarps : 1); }
-template <typename T, int D, bool MASK, bool COPY>
-__global__ void __launch_bounds__(l2_threads<COPY>(), 1)
+template <int CW, int COPY> constexpr int l2_threads() { return CW * 32 + 32 * (COPY ? kL2ProdWarps : 1); }
+template <typename T, int D, bool MASK, bool COPY, int CW>
+__global__ void __launch_bounds__(l2_threads<CW, COPY>(), CW <= 8 ? 2 : 1)
 pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
+  constexpr int kL2ConsWarps = CW;
+  constexpr int kL2Cons = CW * 32;                   // consumer threads = rows per iteration
+  constexpr int kL2StageBoxes = kL2Cons / kL2BoxRows;
+  constexpr int kL2StageBytes = kL2Cons * kL2Tile;   // CW = 16: 32 KiB = 8 boxes; CW = 8: 16 KiB
   extern __shared__ __align__(1024) unsigned char l2_smem_raw[];
   float* lut = reinterpret_cast<float*>(l2_smem_raw);
   unsigned char* ring = l2_smem_raw + (size_t)a.E * (kL2Tile * 4);
@@ -299,6 +308,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   const uint32_t full0 = l2_smem(bars), empty0 = full0 + 8 * kL2MaxStages;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (a.early_ld) pdl_launch_dependents();
   const bool clustered = a.CS > 1;
   const int rank = clustered ? (int)l2_cluster_rank() : 0;
   const int tok = blockIdx.y;
@@ -436,7 +446,10 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       caddr[v] = l2_smem(ring) + (uint32_t)tid * kL2Tile + (((v + lc) & 3) << 4) + 8 * lh;
     // x: this thread's word of the B-fragment layout
     constexpr int XW = l2_x_words<D>();
-    int xoff = tid < XW ? l2_x_offset<D>(tid, tile0, a.M) : -1;
+    constexpr int XF = XW > kL2Cons ? XW / kL2Cons : 1;      // fragment words per thread
+    int xoff[XF];
+#pragma unroll
+    for (int f = 0; f < XF; ++f) xoff[f] = tid + f * kL2Cons < XW ? l2_x_offset<D>(tid + f * kL2Cons, tile0, a.M) : -1;
     int xstep = a.CS * (kL2Tile / a.M) * D;        // elements between this CTA's consecutive tiles
     const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
     uint32_t* xs_mine = reinterpret_cast<uint32_t*>(xs) + tid;
@@ -447,7 +460,9 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     for (int i = 0; i < 4; ++i) {
       asm volatile("" : "+r"(sel[i]), "+r"(colv[i][0]), "+r"(colv[i][1]), "+r"(caddr[i]));
     }
-    asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xoff), "+r"(xstep), "+r"(perm), "+l"(xg), "+l"(xs_mine));
+#pragma unroll
+    for (int f = 0; f < XF; ++f) asm volatile("" : "+r"(xoff[f]));
+    asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xstep), "+r"(perm), "+l"(xg), "+l"(xs_mine));
 
     // codes of one item (row iteration `it` of a tile) -> registers; the stage is released at once
     int stage = 0, round = 0;
@@ -493,36 +508,42 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     l2_trace(a, 2);
 
     // ---- x of this CTA's tiles -> shared memory, B-fragment order (zero beyond K) ----
-    if (tid < XW) {
-      for (int s = 0; s < my_tiles; ++s) {
-        const int elem = xoff + s * xstep;
-        uint32_t v = 0u;
-        if (xoff >= 0 && elem < a.K) {
-          v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
-          // x is [T, 2K] = (gate | up): SiLU(gate) * up on the way in (llama.py:89-93)
-          if (a.xact) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+#pragma unroll
+    for (int f = 0; f < XF; ++f) {
+      if (tid + f * kL2Cons < XW) {
+        for (int s = 0; s < my_tiles; ++s) {
+          const int elem = xoff[f] + s * xstep;
+          uint32_t v = 0u;
+          if (xoff[f] >= 0 && elem < a.K) {
+            v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
+            // x is [T, 2K] = (gate | up): SiLU(gate) * up on the way in (llama.py:89-93)
+            if (a.xact) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+          }
+          xs_mine[s * XW + f * kL2Cons] = v;
         }
-        xs_mine[s * XW] = v;
       }
     }
     l2_trace(a, 11);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
     l2_trace(a, 12);
-    l2_cons_sync();
+    l2_cons_sync<kL2Cons>();
     l2_trace_dep(a, 3, reinterpret_cast<const volatile uint32_t*>(xs) + 255);
 
     for (int s = 0; s < my_tiles; ++s) {
-      if (s > 0) l2_cons_sync();                   // everyone is done with the previous table
-      l2_build_table<T, D>(lut, cbs, xs + (size_t)s * l2_x_words<D>() * 2, a.E, a.M, warp, lane);
+      if (s > 0) l2_cons_sync<kL2Cons>();                   // everyone is done with the previous table
+      l2_build_table<T, D, CW>(lut, cbs, xs + (size_t)s * l2_x_words<D>() * 2, a.E, a.M, warp, lane);
       if (s == 0) l2_trace(a, 10);
-      l2_cons_sync();
+      l2_cons_sync<kL2Cons>();
       if (s == 0) l2_trace_dep(a, 4, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
+      if (s == 1) l2_trace_dep(a, 13, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
       if (s + 1 == my_tiles && clustered) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
       for (int it = 0; it < n_iter; ++it) {
         uint32_t cw[4][4];
         load_codes(cw, it);
         lookups(cw, s, it);
         if (s == 0 && it == 0) l2_trace(a, 9);
+        if (s == 1 && it == 0) l2_trace(a, 14);
+        if (s == 0 && it == n_iter - 1) l2_trace(a, 15);
       }
     }
     if (my_tiles == 0) {                           // no tile in this K group: contribute zeros
@@ -554,7 +575,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     __syncthreads();
   }
   l2_trace(a, 6);
-  for (int i = fin0 + tid; i < fin1; i += l2_threads<COPY>()) {
+  for (int i = fin0 + tid; i < fin1; i += l2_threads<CW, COPY>()) {
     const int row = rb.row0 + i;
     float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
     float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
@@ -584,7 +605,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     __syncthreads();
     if (*last_flag) {
       __threadfence();
-      for (int i = fin0 + tid; i < fin1; i += l2_threads<COPY>()) {
+      for (int i = fin0 + tid; i < fin1; i += l2_threads<CW, COPY>()) {
         const int row = rb.row0 + i;
         float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
         float b = Traits<T>::to_f(*reinterpret_cast<const T*>(&bi0_raw));
@@ -607,43 +628,51 @@ extern unsigned long long* g_lut_trace;
 extern int g_lut_last_grid[4];
 
 struct Lut2Plan {
-  int cs, S, kg, n_tiles, rows_per_cluster, stages, smem_cb, smem_x, smem_total;
+  int cw, cs, S, kg, n_tiles, rows_per_cluster, stages, smem_cb, smem_x, smem_total;
 };
 
-static int lut2_smem_bytes(int E, int stages, int smem_cb, int smem_x, int rows) {
-  return E * kL2Tile * 4 + stages * kL2StageBytes + smem_cb + smem_x + (2 * rows + kL2MaxCluster) * 4 +
+static int lut2_smem_bytes(int E, int stages, int cw, int smem_cb, int smem_x, int rows) {
+  return E * kL2Tile * 4 + stages * cw * 32 * kL2Tile + smem_cb + smem_x + (2 * rows + kL2MaxCluster) * 4 +
          2 * 8 * kL2MaxStages + 16;                // mbarriers + the K-group ticket flag
 }
 
-constexpr int kL2TwoPerSm = 113 * 1024;            // two CTAs (this layer's + the next layer's) fit one SM
+constexpr int kL2TwoPerSm = 112 * 1024;            // two CTAs (this layer's + the next layer's) fit one SM:
+                                                   // 228 KiB - 2 x (1 KiB static + 1 KiB reserved)
 
-// Co-resident clusters of `cs` CTAs at `smem` bytes per CTA (GPC granularity strands a few SMs
-// for cs >= 4).  Without a device: B200 figures.
-static int lut2_cluster_slots(int cs, int smem) {
-  static int cache[16][4][64] = {};                // device, log2(cs), smem / 4 KiB
+static int lut2_log2(int cs) { return cs == 1 ? 0 : cs == 2 ? 1 : cs == 4 ? 2 : cs == 8 ? 3 : 4; }
+
+template <int CW>
+static int lut2_query_clusters(int cs, int smem) {
+  auto kern = pq_gemv_lut2_kernel<__half, 8, false, false, CW>;
+  int n = -1;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) != cudaSuccess) return -1;
+  if (cs > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) return -1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(l2_threads<CW, false>()); cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) n = -1;
+  return n;
+}
+
+// Co-resident clusters of `cs` CTAs of shape `cw` at `smem` bytes per CTA (GPC granularity strands
+// a few SMs for cs >= 4).  Without a device: B200 figures.
+static int lut2_cluster_slots(int cw, int cs, int smem) {
+  static int cache[16][2][5][64] = {};             // device, shape, log2(cs), smem / 4 KiB
   int dev = 0;
   const bool have_dev = cudaGetDevice(&dev) == cudaSuccess && dev < 16;
-  const int l2 = cs == 1 ? 0 : cs == 2 ? 1 : cs == 4 ? 2 : 3, sb = min(63, smem / 4096);
-  if (have_dev && cache[dev][l2][sb] > 0) return cache[dev][l2][sb];
+  const int l2 = lut2_log2(cs), sb = min(63, smem / 4096), w = cw == 8 ? 0 : 1;
+  if (have_dev && cache[dev][w][l2][sb] > 0) return cache[dev][w][l2][sb];
   int n = -1;
-  if (have_dev) {
-    auto kern = pq_gemv_lut2_kernel<__half, 8, false, false>;
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) == cudaSuccess) {
-      cudaLaunchConfig_t cfg{};
-      cfg.gridDim = dim3(cs * 1024, 1, 1); cfg.blockDim = dim3(l2_threads<false>()); cfg.dynamicSmemBytes = (sb + 1) * 4096;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr; cfg.numAttrs = 1;
-      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) n = -1;
-    }
-  }
+  if (have_dev) n = cw == 8 ? lut2_query_clusters<8>(cs, (sb + 1) * 4096) : lut2_query_clusters<16>(cs, (sb + 1) * 4096);
   if (n <= 0) {
     cudaGetLastError();
-    static const int one[4] = {148, 74, 33, 15}, two[4] = {296, 148, 71, 33};
-    n = smem <= kL2TwoPerSm ? two[l2] : one[l2];
+    static const int one[5] = {148, 74, 33, 15, 7}, two[5] = {296, 148, 71, 33, 15};
+    n = (cw == 8 && smem <= kL2TwoPerSm) ? two[l2] : one[l2];
   }
-  if (have_dev) cache[dev][l2][sb] = n;
+  if (have_dev) cache[dev][w][l2][sb] = n;
   return n;
 }
 
@@ -657,64 +686,107 @@ static int64_t lut2_blocks(const int64_t* part_sizes, int n_parts, int64_t n, in
 constexpr int kL2MaxKG = 8;                        // K groups (clusters along K) per row block
 constexpr int kL2TicketBytes = 64 * 1024;          // head of the workspace (include/pq_b200.h)
 
-// Cluster size CS, tiles per CTA S, K groups KG (CS * S * KG >= n_tiles) and rows per row block
-// from a small cycle model calibrated on B200 phase traces (profiles/r1_1x_trace_lut_tma*.txt):
-// a CTA pays a fixed cost, ~2500 cycles per table build and ~1900 per 512-row iteration of
-// lookups; a cluster reduce costs ~1200, the cross-cluster (workspace + ticket) reduce ~3000.
-// One CTA per SM (16 + 1 warps, > 113 KiB of shared memory).
+static int lut2_env(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? (int)strtol(e, nullptr, 0) : dflt;
+}
+
+// CTA shape CW, cluster size CS, tiles per CTA S, K groups KG (CS * S * KG >= n_tiles) and rows per
+// row block from a small cycle model calibrated on B200 phase traces (profiles/): a CTA pays a
+// fixed cost, a cost per table build and one per row iteration of lookups; a cluster reduce costs
+// ~1200 cycles, the cross-cluster (workspace + ticket) reduce ~3000.
+//   CW = 16: one CTA per SM.   CW = 8: planned at `per_sm8` CTAs of this launch per SM (1: the
+//   other half of the SM is left to the next layer's CTA, whose prologue then overlaps this
+//   layer under programmatic dependent launch; 2: both halves work on this layer).
 static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
-                      const int64_t* part_sizes, int n_parts) {
+                      const int64_t* part_sizes, int n_parts, bool allow_kg = true) {
   const int E = 1 << nbits;
   const int64_t gp = k / d * m;
   pl.n_tiles = (int)((gp + kL2Tile - 1) / kL2Tile);
   pl.smem_cb = m * E * d * 2;
-  static const int force_cs = [] { const char* e = getenv("PQ_LUT2_CS"); return e ? atoi(e) : 0; }();
-  static const int force_kg = [] { const char* e = getenv("PQ_LUT2_KG"); return e ? atoi(e) : 0; }();
-  static const int force_stages = [] { const char* e = getenv("PQ_LUT2_STAGES"); return e ? atoi(e) : 0; }();
+  static const int force_cw = lut2_env("PQ_LUT2_CW", 0), force_cs = lut2_env("PQ_LUT2_CS", 0);
+  static const int force_kg = lut2_env("PQ_LUT2_KG", 0), force_stages = lut2_env("PQ_LUT2_STAGES", 0);
+  static const int per_sm8 = lut2_env("PQ_LUT2_PER_SM8", 1);
+  static const int fixed8 = lut2_env("PQ_LUT2_FIXED8", 3000), fixed16 = lut2_env("PQ_LUT2_FIXED16", 5000);
+  static const int build8 = lut2_env("PQ_LUT2_BUILD8", 2500), item8 = lut2_env("PQ_LUT2_ITEM8", 1100);
   const int sms = sm_count();
   double best = 1e30;
   bool found = false;
-  for (int cs = 1; cs <= kL2MaxCluster; cs *= 2) {
-    if (cs > pl.n_tiles) break;
-    if (force_cs && cs != force_cs) continue;
-    int slots1 = lut2_cluster_slots(cs, 200 * 1024);           // one CTA per SM
-    if (slots1 * cs > sms) slots1 = sms / cs;
-    for (int kg = 1; kg <= kL2MaxKG; ++kg) {
-      if (force_kg && kg != force_kg) continue;
-      const int S = (pl.n_tiles + cs * kg - 1) / (cs * kg);
-      if ((kg - 1) * cs * S >= pl.n_tiles) continue;           // the last K group would be empty
-      const int smem_x = S * (d == 16 ? 512 : 256) * 4;        // B-fragment order, see l2_x_offset
-      if (smem_x > 32 * 1024) continue;
-      int target = slots1 / (int)(t * kg);                     // row blocks in one wave
-      if (target < 1) target = 1;
-      int rows = (int)((n + target - 1) / target);
-      rows = (rows + kL2BoxRows - 1) / kL2BoxRows * kL2BoxRows;
-      const int max_rows = 4096;
-      if (rows > max_rows) rows = max_rows;
-      while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
-      const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
-      int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(kL2MaxStages, max(2, S * n_iter));
-      auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, pl.smem_cb, smem_x, rows); };
-      while (stages > 2 && smem_of(stages) > 220 * 1024) --stages;
-      const int smem = smem_of(stages);
-      if (smem > 220 * 1024) continue;
-      const int64_t clusters = lut2_blocks(part_sizes, n_parts, n, rows) * kg * t;
-      if (clusters * cs > 65535 * 8) continue;
-      const int64_t waves = (clusters + slots1 - 1) / slots1;
-      // narrower clusters stream narrower strips of the code matrix and measured ~20 % slower per
-      // row iteration; K groups only where they clearly pay (profiles/r1_18_microbench_lut_tma.jsonl)
-      const double item = 1900.0 * (cs < 8 ? 1.2 : 1.0);
-      const double cta = 5000.0 + (cs > 1 ? 1200.0 : 0.0) + (kg > 1 ? 3000.0 : 0.0) +
-                         S * (2500.0 * E / 256.0 + (rows / 512.0 + 0.3) * item);
-      const double cost = (double)waves * cta * (kg > 1 ? 1.15 : 1.0);
-      if (cost < best) {
-        best = cost; found = true;
-        pl.cs = cs; pl.S = S; pl.kg = kg; pl.rows_per_cluster = rows; pl.stages = stages;
-        pl.smem_x = smem_x; pl.smem_total = smem;
+  for (int cw = 8; cw <= 16; cw += 8) {
+    if (force_cw && cw != force_cw) continue;
+    const int cons = cw * 32;
+    const int smem_cap = cw == 8 ? kL2TwoPerSm : 220 * 1024;
+    for (int cs = 1; cs <= kL2MaxCluster; cs *= 2) {
+      if (cs > pl.n_tiles) break;
+      if (force_cs && cs != force_cs) continue;
+      if (cs == 16 && !force_cs && cw == 16) continue;           // 16-CTA clusters: the small shape only
+      int slots1 = lut2_cluster_slots(cw, cs, cw == 8 ? 100 * 1024 : 200 * 1024);
+      const int per_sm = cw == 8 ? per_sm8 : 1;
+      if (slots1 * cs > sms * per_sm) slots1 = sms * per_sm / cs;
+      if (slots1 < 1) continue;
+      for (int kg = 1; kg <= (allow_kg ? kL2MaxKG : 1); ++kg) {
+        if (force_kg && kg != force_kg && allow_kg) continue;
+        const int S = (pl.n_tiles + cs * kg - 1) / (cs * kg);
+        if ((kg - 1) * cs * S >= pl.n_tiles) continue;           // the last K group would be empty
+        const int smem_x = S * (d == 16 ? 512 : 256) * 4;        // B-fragment order, see l2_x_offset
+        if (smem_x > 32 * 1024) continue;
+        int target = slots1 / (int)(t * kg);                     // row blocks in one wave
+        if (target < 1) target = 1;
+        int rows = (int)((n + target - 1) / target);
+        rows = (rows + kL2BoxRows - 1) / kL2BoxRows * kL2BoxRows;
+        const int max_rows = 4096;
+        if (rows > max_rows) rows = max_rows;
+        while (rows < max_rows && lut2_blocks(part_sizes, n_parts, n, rows) > target) rows += kL2BoxRows;
+        const int n_iter = (rows + cons - 1) / cons;
+        // measured on B200 (gpurun r2_01, profiles/r2_01_*): the 8-warp CTA wins only where a CTA has a
+        // single item (o_proj: 4.6 against 5.0 us); with more items its half-size lookup crew loses
+        // more than the co-resident prologue gains (qkv 6.7 / 6.3, gate_up 8.7 / 7.6, down 9.2 / 8.1 us)
+        if (cw == 8 && !force_cw && S * n_iter > 1) continue;
+        int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(cw == 8 ? kL2MaxStages : 4, max(2, S * n_iter));
+        auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, cw, pl.smem_cb, smem_x, rows); };
+        while (stages > (cw == 8 ? 1 : 2) && smem_of(stages) > smem_cap) --stages;
+        const int smem = smem_of(stages);
+        if (smem > smem_cap) continue;
+        const int64_t clusters = lut2_blocks(part_sizes, n_parts, n, rows) * kg * t;
+        if (clusters * cs > 65535 * 8) continue;
+        const int64_t waves = (clusters + slots1 - 1) / slots1;
+        // narrower clusters stream narrower strips of the code matrix and measured ~20 % slower per
+        // row iteration; K groups only where they clearly pay (profiles/r1_18_microbench_lut_tma.jsonl)
+        double cta;
+        if (cw == 16) {
+          const double item = 1900.0 * (cs < 8 ? 1.2 : 1.0);
+          cta = fixed16 + (cs > 1 ? 1200.0 : 0.0) + (kg > 1 ? 3000.0 : 0.0) +
+                S * (2500.0 * E / 256.0 + (rows / 512.0 + 0.3) * item);
+        } else {
+          const double item = item8 * (cs < 8 ? 1.2 : 1.0) * (per_sm == 2 ? 1.6 : 1.0);
+          cta = fixed8 + (per_sm == 2 ? fixed16 - fixed8 : 0) + (cs > 1 ? 1200.0 : 0.0) + (cs > 8 ? 400.0 : 0.0) +
+                (kg > 1 ? 3000.0 : 0.0) + S * (build8 * E / 256.0 + (rows / 256.0 + 0.3) * item);
+        }
+        const double cost = (double)waves * cta * (kg > 1 ? 1.15 : 1.0);
+        if (cost < best) {
+          best = cost; found = true;
+          pl.cw = cw; pl.cs = cs; pl.S = S; pl.kg = kg; pl.rows_per_cluster = rows; pl.stages = stages;
+          pl.smem_x = smem_x; pl.smem_total = smem;
+        }
       }
     }
   }
   return found;
+}
+
+int gemv_lut2_debug_slots(int cw, int cs, int smem) {
+  return cw == 8 ? lut2_query_clusters<8>(cs, smem) : lut2_query_clusters<16>(cs, smem);
+}
+
+// {cw, cs, S, kg, rows per cluster, stages, smem bytes, n_tiles, grid.x} of the plan (diagnostics, tests)
+int gemv_lut2_debug_plan(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                         int n_parts, int* out9) {
+  Lut2Plan pl;
+  if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts)) return PQ_ERR_UNSUPPORTED;
+  const int v[9] = {pl.cw, pl.cs, pl.S, pl.kg, pl.rows_per_cluster, pl.stages, pl.smem_total, pl.n_tiles,
+                    (int)(lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.kg * pl.cs)};
+  for (int i = 0; i < 9; ++i) out9[i] = v[i];
+  return PQ_OK;
 }
 
 // Upper bound for every plan (the plan may depend on the partition sizes): tickets + KG partials.
@@ -772,20 +844,22 @@ static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-template <typename T, int D, bool MASK, bool COPY>
+template <typename T, int D, bool MASK, bool COPY, int CW>
 static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY>;
+  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY, CW>;
   static bool attr_set[64] = {};                   // per instantiation, per device
   int dev = 0;
   cudaGetDevice(&dev);
   if (!attr_set[dev & 63]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
     if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) return (int)e;
     attr_set[dev & 63] = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.kg * pl.cs, a.T, 1);
-  cfg.blockDim = dim3(l2_threads<COPY>());
+  cfg.blockDim = dim3(l2_threads<CW, COPY>());
   cfg.dynamicSmemBytes = pl.smem_total;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
@@ -794,15 +868,20 @@ static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl
   attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 2 : 1;
-  g_lut_last_grid[0] = cfg.gridDim.x; g_lut_last_grid[1] = cfg.gridDim.y;
-  g_lut_last_grid[2] = pl.cs; g_lut_last_grid[3] = pl.smem_total;
+  if (a.trace) {                                   // diagnostics only (tools/trace_lut.py)
+    g_lut_last_grid[0] = cfg.gridDim.x; g_lut_last_grid[1] = cfg.gridDim.y;
+    g_lut_last_grid[2] = pl.cs; g_lut_last_grid[3] = pl.smem_total;
+  }
   return (int)cudaLaunchKernelEx(&cfg, kern, map, a);
 }
 
 template <typename T, int D, bool MASK>
 static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  return a.copy_w ? launch_lut2_c<T, D, MASK, true>(map, a, pl, stream)
-                  : launch_lut2_c<T, D, MASK, false>(map, a, pl, stream);
+  if (pl.cw == 8)
+    return a.copy_w ? launch_lut2_c<T, D, MASK, true, 8>(map, a, pl, stream)
+                    : launch_lut2_c<T, D, MASK, false, 8>(map, a, pl, stream);
+  return a.copy_w ? launch_lut2_c<T, D, MASK, true, 16>(map, a, pl, stream)
+                  : launch_lut2_c<T, D, MASK, false, 16>(map, a, pl, stream);
 }
 
 template <typename T>
@@ -828,7 +907,9 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
                        cudaStream_t stream, int xact) {
   if ((uintptr_t)codes % 16 || (uintptr_t)x % 4 || (x_stride * 2) % 4) return PQ_ERR_ALIGN;
   Lut2Plan pl;
-  if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts)) return PQ_ERR_UNSUPPORTED;
+  // K groups meet in the workspace; without one (it is optional) the plan keeps each row block in one cluster
+  const bool have_ws = workspace && workspace_bytes >= kL2TicketBytes + (int64_t)kL2MaxKG * t * n * 4;
+  if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts, have_ws)) return PQ_ERR_UNSUPPORTED;
   Lut2Args a{};
   a.x = x; a.codebooks = codebooks; a.scales = scales; a.bias = bias;
   a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
@@ -851,6 +932,9 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
 
   a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
   a.trace = g_lut_trace; a.xact = xact;
+  static const int early_ld = lut2_env("PQ_LUT2_EARLY_LD", 0);
+  a.early_ld = early_ld;
+  a.trace_mask = lut2_env("PQ_LUT2_TRACE_MASK", 0xffff);
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
   if (rc) return rc;
   CUtensorMap map;
