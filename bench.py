@@ -201,6 +201,46 @@ def time_replays(run, steps, world, device):
     return float(ms.item()) / steps
 
 
+def check_result(model, x_dev, y_dev, world, n_layers=2):
+    """Outside the timed region: the step's result is finite, and every linear of the first
+    `n_layers` decoder layers - fed the input it actually saw in the stack - agrees with the
+    oracle's fp64 evaluation of the same contraction within the P3 bound.  TP > 1:
+    each rank checks its own shard's partial products (apply, before the all-reduce)."""
+    from oracle import pq_oracle as O
+    res = {"finite": bool(torch.isfinite(y_dev).all()), "linears": 0, "max_rms_rel": 0.0}
+    tol = 2e-3 if y_dev.dtype == torch.float16 else 1.6e-2
+    seen = []
+
+    def hook(name):
+        def fn(mod, inp, out):
+            seen.append((name, mod, inp[0].detach().clone()))
+        return fn
+    handles = []
+    for li, layer in enumerate(model.layers[:n_layers]):
+        for name, lin in layer.linears():
+            handles.append(lin.register_forward_hook(hook(f"{li}.{name}")))
+    with torch.no_grad():
+        model(x_dev)
+        for name, lin, xin in seen:
+            k = lin.codes.shape[1] * lin.codebooks.shape[3]
+            xc = xin.cpu()
+            if xin.shape[-1] == 2 * k:                      # --fused-act: down_proj was handed (gate | up)
+                y = lin.quant_method.apply_silu_mul(lin, xin)
+                xc = O.silu_and_mul(xc)
+            else:
+                y = lin.quant_method.apply(lin, xin)
+            parts = list(getattr(lin.codebooks, "output_partition_sizes", []))
+            ref = O.linear_fp32(xc, lin.codes.cpu(), lin.codebooks.cpu(), lin.scales.cpu(), parts, None)
+            err = O.error_report(y.cpu(), ref)
+            res["linears"] += 1
+            res["max_rms_rel"] = max(res["max_rms_rel"], err["rms_rel"])
+    for h in handles:
+        h.remove()
+    res["ok"] = res["finite"] and res["max_rms_rel"] < tol
+    res["tol_rms_rel"] = tol
+    return res
+
+
 def run_gpu_arm(args):
     import vllm_pq_b200 as P
     from vllm_pq_b200 import stack as S
@@ -291,6 +331,14 @@ def run_gpu_arm(args):
             ab = S.algorithmic_bytes(lin, B)
             kernels[name] = {"us": ms_k * 1e3, "algorithmic_bytes": ab, "gbs": ab / (ms_k * 1e-3) / 1e9}
     clocks = clk.summary()
+    checked = check_result(model, x_dev, y_dev, world)      # outside the timed region
+    if world > 1:                                           # every rank must hold the same bits
+        ref_y = y_dev.clone()
+        dist.broadcast(ref_y, src=0)
+        same = torch.tensor([int(torch.equal(ref_y, y_dev) and checked["ok"])], device=device)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        checked["identical_across_ranks_and_ok_on_all"] = bool(same.item())
+        checked["ok"] = checked["ok"] and bool(same.item())
 
     if rank == 0:
         dom = max(kernels, key=lambda k: kernels[k]["us"])
@@ -315,6 +363,7 @@ def run_gpu_arm(args):
                     "h2d_bytes_per_step": x_host.numel() * x_host.element_size(),
                     "d2h_bytes_per_step": y_host.numel() * y_host.element_size()},
             "gpu_launches": model.launches_per_step() * args.steps,
+            "checked": checked["ok"], "check": checked,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                          "frac": achieved / hbm_gbs,

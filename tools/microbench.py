@@ -12,7 +12,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import vllm_pq_b200 as P  # noqa: E402
 from vllm_pq_b200 import _lib  # noqa: E402
 
-HBM_GBS = 6524.6
+HBM_GBS = 6551.4      # MEASURED_PEAKS.json (r2 pool)
 
 try:
     import pynvml
@@ -108,6 +108,7 @@ def main():
     ap.add_argument("--warm", type=float, default=0.3)
     ap.add_argument("--nrep", type=int, default=0)
     ap.add_argument("--ref", type=int, default=0, help="also time the reference's own CUDA kernels (oracle/_ref)")
+    ap.add_argument("--dense", type=int, default=0, help="also time torch.matmul on the dequantised dense weight (cuBLAS)")
     a = ap.parse_args()
     dtype = torch.float16 if a.dtype == "fp16" else torch.bfloat16
     P.ops.set_pdl(bool(a.pdl))
@@ -145,6 +146,13 @@ def main():
                                      gbs=ab / dt / 1e9, frac=ab / dt / 1e9 / HBM_GBS,
                                      tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
                     print(rows[-1], flush=True)
+                if a.dense:
+                    dense = [(P.ops.pq_dequant(s[0], s[1], parts, s[2]),) for s in sets[:max(2, min(len(sets), (512 << 20) // (n * k * 2)))]]
+                    dt = time_loop(lambda s: torch.matmul(x, s[0].t()), dense, 10, graph=bool(a.graph))
+                    rows.append(dict(shape=sname, fmt=f, op="gemm", algo="dense_cublas", t=t, us=dt * 1e6,
+                                     gbs=(n * k * 2) / dt / 1e9, tflops=2 * t * n * k / dt / 1e12, sm_mhz=time_loop.last_clock))
+                    print(rows[-1], flush=True)
+                    del dense
                 if a.ref:
                     from oracle import ref_cuda as R
                     if R.available() and R.supports(b, d, m, dtype):

@@ -72,7 +72,9 @@ pq_allreduce_oneshot_kernel(const uint4* __restrict__ in, uint4* __restrict__ ou
   if (threadIdx.x < WORLD) {
     __threadfence_system();
     st_release_sys(peers.flags[threadIdx.x] + blockIdx.x * WORLD + rank, epoch);
-    while (ld_acquire_sys(my_flags + blockIdx.x * WORLD + threadIdx.x) != epoch) {}
+    // monotonic wait: a peer that already finished this epoch may have overwritten its flag with
+    // epoch + 1 (it can run at most one epoch ahead) - an equality test would then spin forever
+    while ((int32_t)(ld_acquire_sys(my_flags + blockIdx.x * WORLD + threadIdx.x) - epoch) < 0) {}
   }
   __syncthreads();
 

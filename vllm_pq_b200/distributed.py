@@ -42,12 +42,46 @@ def init_tensor_parallel(group: Optional[dist.ProcessGroup] = None, oneshot: Opt
         oneshot = os.environ.get("PQ_ONESHOT_ALLREDUCE", "1") != "0"
     if (oneshot and _TP_WORLD in (2, 4, 8) and torch.cuda.is_available()
             and dist.get_backend(_TP_GROUP) == "nccl"):
+        _ONESHOT = _setup_oneshot(_TP_GROUP, max_oneshot_bytes)
+
+
+def _setup_oneshot(group: dist.ProcessGroup, max_bytes: int) -> Optional["OneShotAllReduce"]:
+    """Peer-memory all-reduce for the whole group or for nobody: a rank that went to NCCL while its
+    peers spin in the NVLink kernel would hang the group, so every step that can fail on one rank
+    only (same node? peer access? cudaIpcOpenMemHandle?) ends in an agreed MIN over the group.
+    Checks follow custom_all_reduce.py:86-147 (single node, full P2P)."""
+    import socket
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    where = [None] * world
+    dist.all_gather_object(where, (socket.gethostname(), torch.cuda.current_device()), group=group)
+    ok, why = True, ""
+    if len({h for h, _ in where}) != 1:
+        ok, why = False, "ranks span more than one node"
+    else:
+        me = torch.cuda.current_device()
+        for r, (_, d) in enumerate(where):
+            if r != rank and (d == me or not torch.cuda.can_device_access_peer(me, d)):
+                ok, why = False, f"no peer access from device {me} to device {d}"
+                break
+    comm = None
+    if _agree(ok, group):
         try:
-            _ONESHOT = OneShotAllReduce(_TP_GROUP, max_oneshot_bytes)
-        except Exception as exc:  # peer access unavailable: NCCL only, said out loud
-            if _TP_RANK == 0:
-                print(f"[vllm_pq_b200] one-shot all-reduce disabled: {exc}")
-            _ONESHOT = None
+            comm = OneShotAllReduce(group, max_bytes)
+        except Exception as exc:                       # noqa: BLE001 - reported below, agreed on by all ranks
+            ok, why = False, str(exc)
+        if not _agree(ok and comm is not None, group):
+            if comm is not None:
+                comm.close()
+            comm = None
+    if comm is None and rank == 0:
+        print(f"[vllm_pq_b200] one-shot all-reduce disabled on every rank ({why or 'a peer could not set it up'}); using NCCL")
+    return comm
+
+
+def _agree(ok: bool, group: dist.ProcessGroup) -> bool:
+    flag = torch.tensor([1 if ok else 0], device="cuda", dtype=torch.int32)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return bool(flag.item())
 
 
 def destroy_tensor_parallel() -> None:
@@ -109,13 +143,24 @@ class OneShotAllReduce:
         self._opened: List[int] = []
         # two staging slots (alternating by the device-side epoch parity) so that a fast
         # rank's next push cannot overwrite data a slow rank is still summing
-        self.data = self._malloc(2 * self.world * self.max_bytes)
-        self.flags = self._malloc(_lib.AR_FLAG_BYTES)
-        stream = torch.cuda.current_stream().cuda_stream
-        _lib.check(self.lib.pq_b200_memset_async(self.flags, 0, _lib.AR_FLAG_BYTES, stream), "memset")
-        torch.cuda.synchronize()
+        self.data = self.flags = None
+        mine = None
+        try:
+            self.data = self._malloc(2 * self.world * self.max_bytes)
+            self.flags = self._malloc(_lib.AR_FLAG_BYTES)
+            stream = torch.cuda.current_stream().cuda_stream
+            _lib.check(self.lib.pq_b200_memset_async(self.flags, 0, _lib.AR_FLAG_BYTES, stream), "memset")
+            torch.cuda.synchronize()
+            mine = (self._handle(self.data), self._handle(self.flags))
+        except Exception as exc:                       # noqa: BLE001 - the collective below must still run
+            mine = None
+            local_error = exc
         handles = [None] * self.world
-        dist.all_gather_object(handles, (self._handle(self.data), self._handle(self.flags)), group=group)
+        dist.all_gather_object(handles, mine, group=group)
+        if mine is None:
+            raise local_error
+        if any(h is None for h in handles):
+            raise RuntimeError("a peer could not allocate its staging buffers")
         self.peer_data = (ctypes.c_void_p * self.world)()
         self.peer_flags = (ctypes.c_void_p * self.world)()
         for r, (hd, hf) in enumerate(handles):
@@ -124,7 +169,8 @@ class OneShotAllReduce:
             else:
                 self.peer_data[r] = self._open(hd)
                 self.peer_flags[r] = self._open(hf)
-        dist.barrier(group=group)
+        # no barrier here: the caller (_setup_oneshot) ends with a group-wide agreement, which also
+        # orders every rank's memset of its flags before any peer's first kernel
 
     def _malloc(self, nbytes: int) -> int:
         p = ctypes.c_void_p()
@@ -163,8 +209,9 @@ class OneShotAllReduce:
             torch.cuda.synchronize()
             for p in self._opened:
                 self.lib.pq_b200_ipc_close_handle(p)
-            self.lib.pq_b200_free(self.data)
-            self.lib.pq_b200_free(self.flags)
+            for p in (self.data, self.flags):
+                if p:
+                    self.lib.pq_b200_free(p)
         except Exception:
             pass
         self._opened = []

@@ -83,10 +83,18 @@ class PQLlamaLinearStack(nn.Module):
     @torch.no_grad()
     def init_synthetic(self, seed: int = 0) -> "PQLlamaLinearStack":
         """Uniform random codes over all entries, signed storage (benchmark_aqlm.py:266-273);
-        Gaussian codebooks scaled so activations stay O(1) through the stack; scales in [0.5, 1.5)."""
+        Gaussian codebooks, zero-mean over the entries and scaled so activations stay O(1) through
+        the stack; scales uniform with E[s^2] = 1.
+
+        Zero mean matters: every row of a PQ weight draws from the same E codewords, so the mean
+        codeword adds the same <cbar, sum_g x_g> to every output.  That common mode feeds the next
+        layer's sum_g x_g and is multiplied by G * |cbar . 1| ~ 1.4 (K = 4096) or 2.3 (K = 11008) per
+        linear: a random walk that overflows fp16 within a few dozen layers (the r1 stack ended
+        non-finite for exactly this reason, profiles/r1_34_bench_act.json "slice_finite")."""
         dev = next(self.parameters()).device
         g = torch.Generator(device=dev).manual_seed(seed)
         e = 1 << self.cfg.nbits_per_codebook
+        s_norm = (1.0 + 1.0 / 12.0) ** -0.5                # rand + 0.5 has E[s^2] = 13/12
         for layer in self.layers:
             for _, lin in layer.linears():
                 k = lin.codes.shape[1] * self.cfg.in_group_size * (
@@ -94,8 +102,9 @@ class PQLlamaLinearStack(nn.Module):
                 lin.codes.data.copy_(torch.randint(-(e // 2), e // 2, lin.codes.shape, device=dev,
                                                    generator=g, dtype=torch.int32))
                 std = (1.0 / (k * self.cfg.num_codebooks)) ** 0.5
-                lin.codebooks.data.copy_(torch.randn(lin.codebooks.shape, device=dev, generator=g) * std)
-                lin.scales.data.copy_(torch.rand(lin.scales.shape, device=dev, generator=g) + 0.5)
+                cb = torch.randn(lin.codebooks.shape, device=dev, generator=g) * std
+                lin.codebooks.data.copy_(cb - cb.mean(dim=1, keepdim=True))
+                lin.scales.data.copy_((torch.rand(lin.scales.shape, device=dev, generator=g) + 0.5) * s_norm)
                 lin.quant_method.process_weights_after_loading(lin)
         return self
 
