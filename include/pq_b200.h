@@ -40,7 +40,7 @@
 extern "C" {
 #endif
 
-#define PQ_B200_ABI_VERSION 1
+#define PQ_B200_ABI_VERSION 2
 #define PQ_MAX_PARTS 8
 
 enum { PQ_F16 = 0, PQ_BF16 = 1 };
@@ -136,6 +136,55 @@ PQ_API int64_t pq_b200_gemm_silu_mul_workspace_bytes(int algo, int64_t t, int64_
  * csrc/torch_bindings.cpp (silu_and_mul).  k even; 16-byte loads when k, strides and pointers allow. */
 PQ_API int pq_b200_silu_and_mul(const void* x, int64_t x_stride, void* out, int64_t out_stride, int64_t t,
                                 int64_t k, int dtype, void* stream);
+
+/* ---- fused epilogue / prologue of the decode table GEMV ------------------------
+ * What the reference runs as separate launches around a row-parallel linear at decode
+ *   apply -> tensor_model_parallel_all_reduce -> fused_add_rms_norm -> next linear
+ *   (vllm/model_executor/layers/linear.py:1209-1213, csrc/custom_all_reduce.cuh:214-237,
+ *    csrc/custom_all_reduce.cu:75-77, csrc/layernorm_kernels.cu:52-98, models/llama.py:272-286)
+ * becomes part of the two GEMV launches it sits between:
+ *   producer (o_proj / down_proj): each finished row is pushed to every peer as one 8-byte
+ *     {fp32 value, epoch} packet, summed in rank order (bitwise identical on all ranks), rounded
+ *     once, added to the residual, stored, and its square added to the CTA's slot of ssq_out;
+ *   consumer (qkv_proj / gate_up_proj): x = RMSNorm(z) * weight on the x load, rstd from norm_ssq.
+ * All fields optional (0 / NULL = off).  Buffers of the all-reduce (per rank, cudaMalloc'd, exchanged
+ * by CUDA IPC like pq_b200_allreduce_oneshot's): ar_peer[r] = rank r's receive buffer of
+ * 2 * ar_world * ar_slot_elems 8-byte packets, zeroed once; ar_state = this rank's 2 x uint32
+ * {epoch, ticket}, zeroed once.  Every rank must issue the same sequence of fused launches. */
+typedef struct {
+  int32_t ar_world, ar_rank;     /* ar_world > 1: all-reduce y over the TP group                */
+  void* const* ar_peer;          /* [ar_world] device pointers (peer-mapped)                     */
+  void* ar_state;
+  int64_t ar_slot_elems;         /* >= t * n                                                     */
+  const void* residual;          /* [t, n] or NULL: y = T(T(sum) + residual)                     */
+  int64_t residual_stride;
+  float* ssq_out;                /* [t, ssq_slots] or NULL: per-CTA sums of y^2                  */
+  int64_t ssq_slots;             /* must equal pq_b200_gemm_fused_slots() of this problem        */
+  const float* norm_ssq;         /* consumer: [t, norm_slots] from the producer, or NULL         */
+  const void* norm_weight;       /* [k] RMSNorm weight; non-NULL turns the norm-on-load on       */
+  int32_t norm_slots;
+  float norm_eps;
+  int32_t input_silu_mul;        /* 1: x is [t, 2k] = (gate | up), the input is SiLU(gate) * up   */
+} pq_b200_epilogue_t;
+
+/* pq_b200_gemm on the table GEMV (PQ_ALGO_GEMV_LUT_TMA) with the extras above; PQ_ERR_UNSUPPORTED when
+ * that kernel does not cover the problem (t > 8, nbits > 8, ...): run the steps separately then
+ * (pq_b200_gemm, pq_b200_allreduce_oneshot, pq_b200_fused_add_rms_norm). */
+PQ_API int pq_b200_gemm_fused(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                              const void* scales, const void* bias, void* y, int64_t y_stride,
+                              int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                              const int64_t* part_sizes, int n_parts, int dtype,
+                              void* workspace, int64_t workspace_bytes, void* stream,
+                              const pq_b200_epilogue_t* ep);
+/* Floats per token of ssq_out for this problem (the launch's CTA count), or PQ_ERR_UNSUPPORTED. */
+PQ_API int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                                        const int64_t* part_sizes, int n_parts, int64_t workspace_bytes);
+/* In place: residual += input (rounded to the dtype), input = RMSNorm(residual) * weight; or, with
+ * residual == NULL, input = RMSNorm(input) * weight.  <- fused_add_rms_norm / rms_norm,
+ * csrc/layernorm_kernels.cu:17-98, same roundings.  One CTA per token. */
+PQ_API int pq_b200_fused_add_rms_norm(void* input, int64_t input_stride, void* residual, int64_t residual_stride,
+                                      const void* weight, float eps, int64_t t, int64_t hidden, int dtype,
+                                      void* stream);
 
 /* 1 if kernel family `algo` covers this problem, else 0 (PQ_ALGO_AUTO: always 1). */
 PQ_API int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m);

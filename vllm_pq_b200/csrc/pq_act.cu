@@ -60,4 +60,63 @@ int silu_and_mul_dispatch(const void* x, int64_t x_stride, void* out, int64_t ou
   return e == cudaSuccess ? PQ_OK : PQ_ERR_DEVICE;
 }
 
+// ---- (residual add +) RMSNorm as its own launch: the unfused form of what the table GEMV does in its
+// epilogue / on its x load, the fallback for the kernels without that fusion, and
+// the drop-in for fused_add_rms_norm / rms_norm (csrc/layernorm_kernels.cu:17-98).  Same roundings:
+// z = T(x + r); variance over float(z); out = T(T(z * rstd) * w).  One CTA per token; the sum of
+// squares is reduced in a fixed order (lane tree, then warps in order).
+constexpr int kNormThreads = 512;
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads) add_rms_norm_kernel(T* __restrict__ input, int64_t in_stride,
+                                                                   T* __restrict__ residual, int64_t res_stride,
+                                                                   const T* __restrict__ weight, float eps, int hidden) {
+  __shared__ float warp_part[kNormThreads / 32];
+  __shared__ float s_rstd;
+  pdl_launch_dependents();
+  pdl_wait();
+  T* x = input + blockIdx.x * in_stride;
+  T* r = residual ? residual + blockIdx.x * res_stride : nullptr;
+  float ss = 0.f;
+  for (int i = threadIdx.x; i < hidden; i += kNormThreads) {
+    T z = x[i];
+    if (r) { z = Traits<T>::from_f(Traits<T>::to_f(z) + Traits<T>::to_f(r[i])); r[i] = z; }
+    const float zf = Traits<T>::to_f(z);
+    ss = fmaf(zf, zf, ss);
+  }
+  ss = warp_sum(ss);
+  if ((threadIdx.x & 31) == 0) warp_part[threadIdx.x >> 5] = ss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < kNormThreads / 32; ++i) tot += warp_part[i];
+    s_rstd = rsqrtf(tot / (float)hidden + eps);
+  }
+  __syncthreads();
+  const float rstd = s_rstd;
+  const T* src = r ? r : x;
+  for (int i = threadIdx.x; i < hidden; i += kNormThreads) {
+    const T scaled = Traits<T>::from_f(Traits<T>::to_f(src[i]) * rstd);
+    x[i] = Traits<T>::from_f(Traits<T>::to_f(scaled) * Traits<T>::to_f(weight[i]));   // T * T, one rounding
+  }
+}
+
+int add_rms_norm_dispatch(void* input, int64_t in_stride, void* residual, int64_t res_stride, const void* weight,
+                          float eps, int64_t t, int64_t hidden, int dtype, cudaStream_t stream) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)t); cfg.blockDim = dim3(kNormThreads); cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 1 : 0;
+  cudaError_t e;
+  if (dtype == PQ_F16)
+    e = cudaLaunchKernelEx(&cfg, add_rms_norm_kernel<__half>, (__half*)input, in_stride, (__half*)residual, res_stride,
+                           (const __half*)weight, eps, (int)hidden);
+  else
+    e = cudaLaunchKernelEx(&cfg, add_rms_norm_kernel<__nv_bfloat16>, (__nv_bfloat16*)input, in_stride,
+                           (__nv_bfloat16*)residual, res_stride, (const __nv_bfloat16*)weight, eps, (int)hidden);
+  return (int)e;
+}
+
 }  // namespace pq

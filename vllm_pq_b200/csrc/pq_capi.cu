@@ -18,7 +18,9 @@ bool gemv_lut_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m
 bool gemv_lut_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemv_lut2_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
                        void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
-                       int, int, void*, int64_t, cudaStream_t, int xact);
+                       int, int, void*, int64_t, cudaStream_t, int xact, const pq_b200_epilogue_t* ep);
+int64_t gemv_lut2_grid_x(int64_t, int64_t, int64_t, int, int, int, const int64_t*, int, int64_t);
+int add_rms_norm_dispatch(void*, int64_t, void*, int64_t, const void*, float, int64_t, int64_t, int, cudaStream_t);
 int silu_and_mul_dispatch(const void*, int64_t, void*, int64_t, int64_t, int64_t, int, cudaStream_t);
 int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
@@ -193,7 +195,7 @@ static int gemm_impl(const void* x, int64_t x_stride, const void* codes, const v
     // the one condition only the dispatcher can see: partition sizes that are not a multiple of
     // the TMA super-row (odd row counts with an odd code pitch) - fall back to the other kernels
     rc = pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
-                                nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact);
+                                nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact, nullptr);
     if (rc != PQ_ERR_UNSUPPORTED) return rc;
     algo = pick_algo_impl(t, n, k, d, nbits, m, false);
     if (xact)      // the dispatcher refused (partition sizes): activation as its own launch
@@ -216,7 +218,7 @@ static int gemm_impl(const void* x, int64_t x_stride, const void* codes, const v
     case PQ_ALGO_GEMV_LUT_TMA:
       if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
-                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact);
+                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact, nullptr);
     case PQ_ALGO_GEMM_MMA:
       if (!pq::gemm_mma_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
       return pq::gemm_mma_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
@@ -258,6 +260,38 @@ int pq_b200_silu_and_mul(const void* x, int64_t x_stride, void* out, int64_t out
   if (!x || !out) return PQ_ERR_NULL;
   if (t <= 0 || k <= 0 || x_stride < 2 * k || out_stride < k) return PQ_ERR_SHAPE;
   return pq::silu_and_mul_dispatch(x, x_stride, out, out_stride, t, k, dtype, (cudaStream_t)stream);
+}
+
+int pq_b200_gemm_fused(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                       const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                       int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                       int n_parts, int dtype, void* workspace, int64_t workspace_bytes, void* stream,
+                       const pq_b200_epilogue_t* ep) {
+  int rc = check_format(n, k, d, nbits, m, part_sizes, n_parts, dtype);
+  if (rc) return rc;
+  if (!x || !codes || !codebooks || !scales || !y) return PQ_ERR_NULL;
+  const int xact = (ep && ep->input_silu_mul) ? 1 : 0;
+  if (t <= 0 || t > INT32_MAX || x_stride < (xact ? 2 * k : k) || y_stride < n) return PQ_ERR_SHAPE;
+  if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
+  if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                                part_sizes, n_parts, dtype, workspace, workspace_bytes, (cudaStream_t)stream, xact, ep);
+}
+
+int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
+                                 const int64_t* part_sizes, int n_parts, int64_t workspace_bytes) {
+  if (check_format(n, k, d, nbits, m, part_sizes, n_parts, PQ_F16)) return PQ_ERR_SHAPE;
+  if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  return pq::gemv_lut2_grid_x(t, n, k, d, nbits, m, part_sizes, n_parts, workspace_bytes);
+}
+
+int pq_b200_fused_add_rms_norm(void* input, int64_t input_stride, void* residual, int64_t residual_stride,
+                               const void* weight, float eps, int64_t t, int64_t hidden, int dtype, void* stream) {
+  if (dtype != PQ_F16 && dtype != PQ_BF16) return PQ_ERR_DTYPE;
+  if (!input || !weight) return PQ_ERR_NULL;
+  if (t <= 0 || hidden <= 0 || input_stride < hidden || (residual && residual_stride < hidden)) return PQ_ERR_SHAPE;
+  return pq::add_rms_norm_dispatch(input, input_stride, residual, residual_stride, weight, eps, t, hidden, dtype,
+                                   (cudaStream_t)stream);
 }
 
 int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems, int dtype,

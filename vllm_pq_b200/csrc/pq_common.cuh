@@ -124,6 +124,17 @@ __device__ __forceinline__ uint32_t silu_mul_pair(uint32_t gate, uint32_t up) {
   return *reinterpret_cast<const uint32_t*>(&r);
 }
 
+// RMSNorm of a pair of packed elements, rounded the way the reference's fused_add_rms_norm is
+// (csrc/layernorm_kernels.cu:91-97: temp *= s_variance rounds to T, temp *= weight rounds to T).
+template <typename T>
+__device__ __forceinline__ uint32_t rms_norm_pair(uint32_t z, float rstd, uint32_t w) {
+  using T2 = typename Traits<T>::T2;
+  const float2 f = Traits<T>::to_f2(z);
+  uint32_t s = Traits<T>::pack(f.x * rstd, f.y * rstd);
+  const T2 r = __hmul2(*reinterpret_cast<const T2*>(&s), *reinterpret_cast<const T2*>(&w));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -82,8 +82,61 @@ struct Lut2Args {
   int xact;               // 1: x is [T, 2K] and the input is SiLU(x[:, :K]) * x[:, K:]
   int early_ld;           // griddepcontrol.launch_dependents at kernel entry (experiment knob)
   int trace_mask;         // which trace slots stamp (a %globaltimer read is slow: few stamps perturb less)
+  // ---- fused epilogue of the row-parallel layers: all-reduce over NVLink peer memory,
+  // residual add, sum of squares for the RMSNorm that follows ----
+  int ar_world, ar_rank;  // ar_world > 1: y = sum over ranks of this rank's scaled partial rows
+  unsigned long long* ar_peer[PQ_AR_MAX_WORLD];   // every rank's receive buffer: [2][world][ar_slot] packets
+  unsigned int* ar_state; // this rank's {epoch counter, CTA ticket}
+  long long ar_slot;      // packets per (parity, source rank)
+  const void* resid;      // [T, N] residual stream or NULL: y = T(T(sum) + resid)   (layernorm_kernels.cu:75-80)
+  long long resid_stride;
+  float* ssq;             // [T, gridDim.x] or NULL: every CTA's sum of y^2 over the rows it stored
+  // ---- RMSNorm on the x load (xact == 2): x = T(T(z * rstd) * w), rstd from the producer's ssq ----
+  const float* nrm_ssq;   // [T, nrm_slots]
+  const void* nrm_w;      // [K]
+  int nrm_slots;
+  float nrm_eps;
   Parts parts;            // cta_end counts clusters
 };
+
+// One 8-byte packet = {fp32 partial row sum, epoch}: data and flag travel in ONE store, so a reader
+// that sees the epoch sees the value (the LL protocol of NCCL) - no fence, no separate flag write.
+__device__ __forceinline__ void l2_st_sys_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long l2_ld_sys_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// This rank's scaled partial sum of (tok, row) -> the sum over all ranks, identical bits on every rank
+// (fp32, rank order 0..world-1: custom_all_reduce.cuh:204-212).  Replaces the store of y, the
+// all-reduce launch and its staging copy (custom_all_reduce.cuh:214-237, custom_all_reduce.cu:75-77,
+// linear.py:1209-1213).  Slot reuse: parity e & 1 was last used by launch e - 2, which every peer
+// has completed before it could push launch e - 1 data, which this rank needed to finish e - 1.
+__device__ __forceinline__ float l2_allreduce_row(const Lut2Args& a, int tok, int row, float v, uint32_t epoch) {
+  const size_t idx = (size_t)tok * a.N + row;
+  const size_t par = (size_t)(epoch & 1u) * a.ar_world;
+  const unsigned long long pkt = ((unsigned long long)epoch << 32) | __float_as_uint(v);
+  for (int p = 1; p < a.ar_world; ++p) {
+    int peer = a.ar_rank + p;
+    if (peer >= a.ar_world) peer -= a.ar_world;
+    l2_st_sys_u64(a.ar_peer[peer] + (par + a.ar_rank) * a.ar_slot + idx, pkt);
+  }
+  const unsigned long long* mine = a.ar_peer[a.ar_rank] + par * a.ar_slot + idx;
+  float tot = 0.f;
+  for (int r = 0; r < a.ar_world; ++r) {
+    float vr = v;
+    if (r != a.ar_rank) {
+      unsigned long long got;
+      do { got = l2_ld_sys_u64(mine + (size_t)r * a.ar_slot); } while ((uint32_t)(got >> 32) != epoch);
+      vr = __uint_as_float((uint32_t)got);
+    }
+    tot += vr;
+  }
+  return tot;
+}
 
 constexpr int kL2TraceSlots = 16;
 __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
@@ -306,6 +359,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   float* recv = rowsum + a.rows_per_cluster;       // [CS][chunk] partial sums pushed by the peers
   unsigned long long* bars = reinterpret_cast<unsigned long long*>(recv + a.rows_per_cluster + kL2MaxCluster);
   const uint32_t full0 = l2_smem(bars), empty0 = full0 + 8 * kL2MaxStages;
+  unsigned int* epoch_smem = reinterpret_cast<unsigned int*>(bars + 2 * kL2MaxStages) + 1;   // word 0: K-group ticket flag
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (a.early_ld) pdl_launch_dependents();
@@ -506,6 +560,19 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     pdl_launch_dependents();                       // the next layer may start fetching its weights
     pdl_wait();                                    // x comes from the previous kernel
     l2_trace(a, 2);
+    // fused all-reduce: this launch's epoch.  The counter is advanced by the last CTA of the previous
+    // fused launch, which has completed by now; parked in shared memory, not in a register that
+    // would live across the lookup loop.
+    if (a.ar_world > 1 && tid == 0)
+      *epoch_smem = *reinterpret_cast<volatile unsigned int*>(a.ar_state) + 1u;
+    // RMSNorm on the x load: rstd from the producer's per-CTA sums of squares, added in a fixed
+    // order by every warp on its own (no barrier; layernorm_kernels.cu:82-88)
+    float rstd = 1.f;
+    if (a.xact == 2) {
+      float ss = 0.f;
+      for (int j = lane; j < a.nrm_slots; j += 32) ss += __ldcg(a.nrm_ssq + (size_t)tok * a.nrm_slots + j);
+      rstd = rsqrtf(warp_sum(ss) / (float)a.K + a.nrm_eps);
+    }
 
     // ---- x of this CTA's tiles -> shared memory, B-fragment order (zero beyond K) ----
 #pragma unroll
@@ -517,7 +584,10 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
           if (xoff[f] >= 0 && elem < a.K) {
             v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
             // x is [T, 2K] = (gate | up): SiLU(gate) * up on the way in (llama.py:89-93)
-            if (a.xact) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+            if (a.xact == 1) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+            // x is the residual stream z: RMSNorm(z) * w on the way in (layernorm_kernels.cu:91-97)
+            else if (a.xact == 2)
+              v = rms_norm_pair<T>(v, rstd, __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const T*>(a.nrm_w) + elem)));
           }
           xs_mine[s * XW + f * kL2Cons] = v;
         }
@@ -575,6 +645,19 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     __syncthreads();
   }
   l2_trace(a, 6);
+  // One finished row: (all-reduce over the TP ranks,) one rounding of y, (residual add,) store.
+  const uint32_t epoch = a.ar_world > 1 ? *epoch_smem : 0u;
+  float ssq_local = 0.f;
+  auto store_row = [&](int row, float v) {
+    float res = 0.f;
+    if (a.resid) res = Traits<T>::to_f(reinterpret_cast<const T*>(a.resid)[(size_t)tok * a.resid_stride + row]);
+    if (a.ar_world > 1) v = l2_allreduce_row(a, tok, row, v, epoch);
+    T out = Traits<T>::from_f(v);
+    if (a.resid) out = Traits<T>::from_f(Traits<T>::to_f(out) + res);   // z = x + residual in T (layernorm_kernels.cu:75-80)
+    reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = out;
+    const float zf = Traits<T>::to_f(out);
+    ssq_local = fmaf(zf, zf, ssq_local);
+  };
   for (int i = fin0 + tid; i < fin1; i += l2_threads<CW, COPY>()) {
     const int row = rb.row0 + i;
     float sc = Traits<T>::to_f(*reinterpret_cast<const T*>(&sc0_raw));
@@ -586,7 +669,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     float sum = 0.f;
     for (int r = 0; r < fin_parts; ++r) sum += fin[r * part_stride + i + fin_off];
     if (a.KG == 1)
-      reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+      store_row(row, fmaf(sum, sc, b));
     else
       __stcg(a.ws_part + ((size_t)tok * a.KG + kg) * a.N + row, sum);
   }
@@ -615,7 +698,32 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         }
         float sum = 0.f;
         for (int g = 0; g < a.KG; ++g) sum += __ldcg(a.ws_part + ((size_t)tok * a.KG + g) * a.N + row);
-        reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = Traits<T>::from_f(fmaf(sum, sc, b));
+        store_row(row, fmaf(sum, sc, b));
+      }
+    }
+  }
+  // ---- this CTA's share of sum(y^2) for the RMSNorm the consumer applies on its x load: warps in
+  // order, then thread 0 in warp order - a fixed order (CTAs that stored nothing write 0) ----
+  if (a.ssq != nullptr) {
+    __syncthreads();                               // everyone is done reading rowsum / recv
+    const float w = warp_sum(ssq_local);
+    if (lane == 0) rowsum[warp] = w;
+    __syncthreads();
+    if (tid == 0) {
+      float tot = 0.f;
+      for (int i = 0; i < l2_threads<CW, COPY>() / 32; ++i) tot += rowsum[i];
+      a.ssq[(size_t)tok * gridDim.x + blockIdx.x] = tot;
+    }
+  }
+  // ---- fused all-reduce: the last CTA of the launch advances this rank's epoch ----
+  if (a.ar_world > 1) {
+    __syncthreads();
+    if (tid == 0) {
+      const unsigned int n_cta = gridDim.x * gridDim.y;
+      if (atomicAdd(a.ar_state + 1, 1u) == n_cta - 1) {
+        a.ar_state[1] = 0u;
+        __threadfence();
+        *reinterpret_cast<volatile unsigned int*>(a.ar_state) = epoch;
       }
     }
   }
@@ -789,6 +897,15 @@ int gemv_lut2_debug_plan(int64_t t, int64_t n, int64_t k, int d, int nbits, int 
   return PQ_OK;
 }
 
+// gridDim.x of the launch (= floats per token of the fused epilogue's ssq output), or a negative error
+int64_t gemv_lut2_grid_x(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                         int n_parts, int64_t workspace_bytes) {
+  Lut2Plan pl;
+  const bool have_ws = workspace_bytes >= kL2TicketBytes + (int64_t)kL2MaxKG * t * n * 4;
+  if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts, have_ws)) return PQ_ERR_UNSUPPORTED;
+  return lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.kg * pl.cs;
+}
+
 // Upper bound for every plan (the plan may depend on the partition sizes): tickets + KG partials.
 int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t, int, int, int, int) {
   return kL2TicketBytes + (int64_t)kL2MaxKG * t * n * 4;
@@ -904,7 +1021,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
                        const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
                        int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
                        int n_parts, int dtype, void* workspace, int64_t workspace_bytes,
-                       cudaStream_t stream, int xact) {
+                       cudaStream_t stream, int xact, const pq_b200_epilogue_t* ep) {
   if ((uintptr_t)codes % 16 || (uintptr_t)x % 4 || (x_stride * 2) % 4) return PQ_ERR_ALIGN;
   Lut2Plan pl;
   // K groups meet in the workspace; without one (it is optional) the plan keeps each row block in one cluster
@@ -932,6 +1049,31 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
 
   a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
   a.trace = g_lut_trace; a.xact = xact;
+  if (ep != nullptr) {
+    const int64_t grid_x = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.kg * pl.cs;
+    if (ep->ar_world > 1) {
+      if (ep->ar_world > PQ_AR_MAX_WORLD || ep->ar_rank < 0 || ep->ar_rank >= ep->ar_world) return PQ_ERR_SHAPE;
+      if (!ep->ar_peer || !ep->ar_state) return PQ_ERR_NULL;
+      if (t * n > ep->ar_slot_elems) return PQ_ERR_WORKSPACE;
+      a.ar_world = ep->ar_world; a.ar_rank = ep->ar_rank; a.ar_slot = ep->ar_slot_elems;
+      a.ar_state = reinterpret_cast<unsigned int*>(ep->ar_state);
+      for (int r = 0; r < ep->ar_world; ++r) {
+        if (!ep->ar_peer[r] || ((uintptr_t)ep->ar_peer[r] & 7)) return PQ_ERR_ALIGN;
+        a.ar_peer[r] = reinterpret_cast<unsigned long long*>(ep->ar_peer[r]);
+      }
+    }
+    if (ep->residual) { a.resid = ep->residual; a.resid_stride = ep->residual_stride; }
+    if (ep->ssq_out) {
+      if (ep->ssq_slots != grid_x) return PQ_ERR_WORKSPACE;       // pq_b200_gemm_fused_slots() of this problem
+      a.ssq = ep->ssq_out;
+    }
+    if (ep->norm_weight) {
+      if (xact || !ep->norm_ssq || ep->norm_slots < 1) return PQ_ERR_NULL;
+      if ((uintptr_t)ep->norm_weight % 4) return PQ_ERR_ALIGN;
+      a.xact = 2; a.nrm_ssq = ep->norm_ssq; a.nrm_w = ep->norm_weight; a.nrm_slots = ep->norm_slots;
+      a.nrm_eps = ep->norm_eps;
+    }
+  }
   static const int early_ld = lut2_env("PQ_LUT2_EARLY_LD", 0);
   a.early_ld = early_ld;
   a.trace_mask = lut2_env("PQ_LUT2_TRACE_MASK", 0xffff);
