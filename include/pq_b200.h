@@ -168,7 +168,7 @@ typedef struct {
 } pq_b200_epilogue_t;
 
 /* pq_b200_gemm on the table GEMV (PQ_ALGO_GEMV_LUT_TMA) with the extras above; PQ_ERR_UNSUPPORTED when
- * that kernel does not cover the problem (t > 8, nbits > 8, ...): run the steps separately then
+ * pq_b200_gemm_fused_supported() is 0 (t > 8, nbits != 8, ...): run the steps separately then
  * (pq_b200_gemm, pq_b200_allreduce_oneshot, pq_b200_fused_add_rms_norm). */
 PQ_API int pq_b200_gemm_fused(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
                               const void* scales, const void* bias, void* y, int64_t y_stride,
@@ -176,7 +176,9 @@ PQ_API int pq_b200_gemm_fused(const void* x, int64_t x_stride, const void* codes
                               const int64_t* part_sizes, int n_parts, int dtype,
                               void* workspace, int64_t workspace_bytes, void* stream,
                               const pq_b200_epilogue_t* ep);
-/* Floats per token of ssq_out for this problem (the launch's CTA count), or PQ_ERR_UNSUPPORTED. */
+/* 1 if pq_b200_gemm_fused covers the problem (1..8 tokens, 8-bit codes, shapes of the table GEMV). */
+PQ_API int pq_b200_gemm_fused_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+/* Floats per token of ssq_out for this problem (the CTAs that finish rows), or PQ_ERR_UNSUPPORTED. */
 PQ_API int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
                                         const int64_t* part_sizes, int n_parts, int64_t workspace_bytes);
 /* In place: residual += input (rounded to the dtype), input = RMSNorm(residual) * weight; or, with

@@ -198,6 +198,21 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
     return F.silu(x[..., :d]) * x[..., d:]
 
 
+def fused_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
+                       eps: float):
+    """(out, new_residual) of the reference's fused_add_rms_norm / rms_norm kernels
+    (csrc/layernorm_kernels.cu:17-44 and :52-98; called from layers/layernorm.py via
+    llama.py:272-283):  z = x + residual rounded to the dtype (:75-80, packed half add);
+    variance = mean of float(z)^2 (:79,:82-88); out = T(T(float(z) * rstd) * weight) (:91-97: two
+    roundings).  The sum of squares is taken in fp64 here - the kernel's fp32 block reduction has no
+    fixed order, so rstd may differ from it in the last fp32 bit."""
+    z = x if residual is None else (x.float() + residual.float()).to(x.dtype)
+    var = z.double().pow(2).mean(-1, keepdim=True)
+    rstd = torch.rsqrt(var + eps).float()
+    out = ((z.float() * rstd).to(x.dtype).float() * weight.float()).to(x.dtype)
+    return out, z
+
+
 def error_report(y: torch.Tensor, y_ref64: torch.Tensor) -> dict:
     """max-abs, max-abs relative to the largest reference output, rms-relative."""
     diff = (y.double() - y_ref64).abs()

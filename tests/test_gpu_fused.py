@@ -1,0 +1,141 @@
+"""The table GEMV's fused prologue / epilogue on one GPU: residual add, per-CTA sums of
+squares, RMSNorm on the x load, and the stand-alone (residual add +) RMSNorm kernel - against the
+oracle's restatement of csrc/layernorm_kernels.cu and against the unfused launches.  The all-reduce
+part of the epilogue needs >= 2 GPUs: tools/tp_check.py (tests/test_gpu_tp.py)."""
+import pytest
+import torch
+
+import vllm_pq_b200 as P
+from oracle import pq_oracle as O
+from tests.test_gpu_parity import RMS_REL_TOL, dev
+from vllm_pq_b200 import _lib
+
+pytestmark = pytest.mark.gpu
+EPS = 1e-5
+
+
+def ulp_close(a, b, dtype, frac_exact=0.98):
+    """Same bits almost everywhere, never more than one ulp apart."""
+    ai, bi = a.view(torch.int16).int(), b.view(torch.int16).int()
+    diff = (ai - bi).abs()
+    assert int(diff.max()) <= 1, int(diff.max())
+    assert float((diff == 0).float().mean()) >= frac_exact, float((diff == 0).float().mean())
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(1, 4096), (5, 8192), (3, 1000)])
+@pytest.mark.parametrize("with_residual", [True, False])
+def test_fused_add_rms_norm_kernel(dtype, shape, with_residual):
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(shape, generator=g).to(dtype)
+    r = torch.randn(shape, generator=g).to(dtype) if with_residual else None
+    w = (torch.rand(shape[1], generator=g) + 0.5).to(dtype)
+    out_ref, z_ref = O.fused_add_rms_norm(x, r, w, EPS)
+    xd, wd = x.cuda(), w.cuda()
+    rd = r.cuda() if with_residual else None
+    P.ops.fused_add_rms_norm(xd, rd, wd, EPS)
+    if with_residual:
+        assert torch.equal(rd.cpu().view(torch.int16), z_ref.view(torch.int16)), "residual stream must be bit-exact"
+    ulp_close(xd.cpu(), out_ref, dtype)
+
+
+CASES = [("o7b", [4096], 4096, (8, 8, 1)), ("down7b", [4096], 11008, (8, 8, 1)), ("o7b_2x8", [4096], 4096, (8, 8, 2)),
+         ("small", [512], 1024, (8, 8, 1)), ("d4", [1024], 2048, (8, 4, 1))]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+@pytest.mark.parametrize("t", [1, 3, 8])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_residual_and_ssq_epilogue(case, t, dtype):
+    _, parts, k, (b, d, m) = case
+    c = O.make_case(parts, k, b, d, m, t=t, dtype=dtype, seed=21, bias=True)
+    c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).to(dtype)
+    g = dev(c)
+    n = sum(parts)
+    res = torch.randn(t, n, dtype=dtype, device="cuda")
+    plain = P.ops.pq_gemm(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"], algo=_lib.ALGO_GEMV_LUT_TMA)
+    y, ssq = P.ops.pq_gemm_fused(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"],
+                                 residual=res, want_ssq=True)
+    assert torch.equal(y, plain + res), "epilogue residual add != separate add (same roundings expected)"
+    want = y.float().pow(2).sum(-1)
+    got = ssq.sum(-1)
+    assert ssq.dtype == torch.float32 and ssq.shape[0] == t
+    assert torch.allclose(got, want, rtol=1e-5), (got, want)
+    # no residual, no ssq: the fused entry point is the plain kernel
+    y0, _ = P.ops.pq_gemm_fused(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"])
+    assert torch.equal(y0, plain)
+    # reproducible
+    y2, ssq2 = P.ops.pq_gemm_fused(g["x"], g["codes"], g["codebooks"], g["scales"], parts, g["bias"],
+                                   residual=res, want_ssq=True)
+    assert torch.equal(y, y2) and torch.equal(ssq, ssq2)
+
+
+NORM_CASES = [("qkv7b", [4096] * 3, 4096, (8, 8, 1)), ("gateup7b", [11008] * 2, 4096, (8, 8, 1)),
+              ("qkv_2x8", [1024, 256, 256], 2048, (8, 8, 2)), ("d16", [2048], 4096, (8, 16, 1))]
+
+
+@pytest.mark.parametrize("case", NORM_CASES, ids=[c[0] for c in NORM_CASES])
+@pytest.mark.parametrize("t", [1, 4])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_rms_norm_on_x_load(case, t, dtype):
+    """producer (K -> hidden, residual add, ssq) -> consumer (RMSNorm on the x load) against the oracle:
+    the consumer's input is the oracle's RMSNorm of the producer's z."""
+    _, parts, hidden, (b, d, m) = case
+    prod = O.make_case([hidden], 2048, 8, 8, 1, t=t, dtype=dtype, seed=31)
+    prod["codebooks"] = (prod["codebooks"].float() / 2048 ** 0.5).to(dtype)
+    gp = dev(prod)
+    res = torch.randn(t, hidden, dtype=dtype, device="cuda")
+    z, ssq = P.ops.pq_gemm_fused(gp["x"], gp["codes"], gp["codebooks"], gp["scales"], [hidden], None,
+                                 residual=res, want_ssq=True)
+    w = (torch.rand(hidden) + 0.5).to(dtype)
+    c = O.make_case(parts, hidden, b, d, m, t=t, dtype=dtype, seed=32)
+    g = dev(c)
+    y, _ = P.ops.pq_gemm_fused(z, g["codes"], g["codebooks"], g["scales"], parts, None,
+                               norm_ssq=ssq, norm_weight=w.cuda(), norm_eps=EPS)
+    xn_ref, _ = O.fused_add_rms_norm(z.cpu(), None, w, EPS)
+    ref = O.linear_fp32(xn_ref, c["codes"], c["codebooks"], c["scales"], parts, None)
+    err = O.error_report(y.cpu(), ref)
+    assert err["rms_rel"] < RMS_REL_TOL[dtype], err
+    # against the separate launches: norm kernel, then the plain table GEMV (rstd may differ in its
+    # last bit between the two reductions, so a few inputs differ by an ulp)
+    xn = z.clone()
+    P.ops.fused_add_rms_norm(xn, None, w.cuda(), EPS)
+    ulp_close(xn.cpu(), xn_ref, dtype)
+    y_sep = P.ops.pq_gemm(xn, g["codes"], g["codebooks"], g["scales"], parts, None, algo=_lib.ALGO_GEMV_LUT_TMA)
+    err2 = O.error_report(y.cpu(), y_sep.double().cpu())
+    assert err2["rms_rel"] < RMS_REL_TOL[dtype] / 2, err2
+
+
+def test_layer_api_fused_chain_matches_separate_launches():
+    """RowParallelLinear(residual, want_ssq) -> ColumnParallelLinear(input_norm) == the reference's chain
+    apply -> (+ residual) -> RMSNorm -> apply, within tolerance; 16-token batch takes the unfused path."""
+    dtype = torch.float16
+    cfg = P.PQConfig(8, 8, 1, 1)
+    kw = dict(bias=False, params_dtype=dtype, quant_config=cfg)
+    with torch.device("cuda"):
+        o = P.RowParallelLinear(4096, 4096, **kw)
+        gu = P.MergedColumnParallelLinear(4096, [11008, 11008], **kw)
+    gen = torch.Generator(device="cuda").manual_seed(5)
+    for lin in (o, gu):
+        lin.codes.data.copy_(torch.randint(-128, 128, lin.codes.shape, device="cuda", generator=gen, dtype=torch.int32))
+        cb = torch.randn(lin.codebooks.shape, device="cuda", generator=gen) / 64
+        lin.codebooks.data.copy_(cb - cb.mean(1, keepdim=True))
+        lin.scales.data.copy_(torch.rand(lin.scales.shape, device="cuda", generator=gen) + 0.5)
+    w = (torch.rand(4096, device="cuda") + 0.5).to(dtype)
+    for t in (1, 4, 16):
+        x = torch.randn(t, 4096, dtype=dtype, device="cuda")
+        res = torch.randn(t, 4096, dtype=dtype, device="cuda")
+        z, _, ssq = o(x, residual=res, want_ssq=True)
+        y, _ = gu(z, input_norm=(ssq, w, EPS))
+        # separate launches
+        h, _ = o(x)
+        z_ref = h + res
+        xn = z_ref.clone()
+        P.ops.fused_add_rms_norm(xn, None, w, EPS)
+        y_ref, _ = gu(xn)
+        if t == 4:        # separate launches use the mma.sync kernel at 2..16 tokens: same sums, other rounding
+            assert float((z.float() - z_ref.float()).abs().max()) < 2e-2
+        else:
+            assert torch.equal(z, z_ref)
+        rel = float((y.double() - y_ref.double()).pow(2).mean().sqrt() / y_ref.double().pow(2).mean().sqrt())
+        assert rel < 1e-3, (t, rel)

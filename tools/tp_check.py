@@ -5,9 +5,11 @@
 
 1. one-shot NVLink all-reduce (csrc/pq_allreduce.cu) == NCCL all-reduce, bit for bit across ranks,
    eager and under CUDA-graph replay, for decode-sized messages;
-2. a TP = N decoder-layer stack (column-parallel qkv / gate_up, row-parallel o / down + reduce),
-   loaded through the weight loaders from FULL tensors, reproduces the TP = 1 result computed on
-   rank 0's GPU from the same tensors, within the fp16 tolerance of the parity tests.
+2. the TP = N linears of a decoder layer (column-parallel qkv / gate_up, row-parallel o / down),
+   loaded through the weight loaders from FULL tensors, against the ORACLE's fp64 contraction over
+   the full tensors: plain, with the all-reduce fused into the GEMV epilogue (+ residual add + sum
+   of squares), RMSNorm and SiLU*mul on the x loads; bitwise identical across ranks; fused ==
+   separate launches within fp16 rounding; CUDA-graph replay of the fused chain == eager.
 Exit code 0 and one "TP_CHECK PASS" line from rank 0 on success.
 """
 import os
@@ -67,20 +69,45 @@ def main():
         ok = False
         print(f"[rank {rank}] graph-replayed all-reduce mismatch")
 
-    # ---- 2. TP stack vs TP = 1 ----
+    # ---- 2. TP decoder-layer linears against the ORACLE (fp64 contraction over the FULL tensors) ----
+    # hidden 2048, intermediate 5632: at TP = 8 down_proj's shard has 88 code bytes per row (not a
+    # multiple of 16: the cp.async loader), o_proj's 32 (a single partial tile).
+    EPS = 1e-5
+    hidden, head, heads, kv_heads, inter = 2048, 128, 16, 8, 5632
+    dt = torch.float16
+    tol = 2e-3
+
+    def gather_cols(x):                               # [t, w] per rank -> [t, world * w]
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x.contiguous())
+        return torch.cat(parts, -1)
+
+    def same_on_all_ranks(x):
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x.contiguous())
+        return all(torch.equal(parts[0], q) for q in parts)
+
+    def report(name, got, ref64, extra=""):
+        nonlocal ok
+        err = O.error_report(got.cpu(), ref64)
+        good = err["rms_rel"] < tol
+        if not good:
+            ok = False
+        if not good or rank == 0:
+            print(f"[rank {rank}] tp{world} {name}{extra}: rms_rel vs oracle {err['rms_rel']:.2e} {'ok' if good else 'FAIL'}")
+
     for (b, d, m) in ((8, 8, 1), (8, 8, 2), (16, 8, 1)):
-        hidden, head, heads, kv_heads, inter = 1024, 64, 16, 8, 2048
-        dt = torch.float16
         cfg = P.PQConfig(d, b, m, 1)
         kw = dict(bias=False, params_dtype=dt, quant_config=cfg)
-        full = {name: O.make_case(parts, k, b, d, m, t=4, dtype=dt, seed=sd)
+        full = {name: O.make_case(parts, k, b, d, m, t=16, dtype=dt, seed=sd)
                 for sd, (name, parts, k) in enumerate((("q", [heads * head], hidden), ("k", [kv_heads * head], hidden),
                                                        ("v", [kv_heads * head], hidden), ("o", [hidden], heads * head),
                                                        ("gate", [inter], hidden), ("up", [inter], hidden),
                                                        ("down", [hidden], inter)))}
-        for c in full.values():                   # keep activations O(1) through the four linears (fp16 range)
+        for c in full.values():                   # zero-mean codebooks, activations O(1) (stack.py init_synthetic)
             kdim = c["codes"].shape[1] * d
-            c["codebooks"] = (c["codebooks"].float() / (kdim * m) ** 0.5).to(dt)
+            cb = c["codebooks"].float() / (kdim * m) ** 0.5
+            c["codebooks"] = (cb - cb.mean(1, keepdim=True)).to(dt)
         with torch.device(dev):
             qkv = P.QKVParallelLinear(hidden, head, heads, kv_heads, **kw)
             o = P.RowParallelLinear(heads * head, hidden, **kw)
@@ -93,31 +120,75 @@ def main():
                 p = getattr(gu, name); p.weight_loader(p, full[key][name].to(dev), sid)
             for layer, key in ((o, "o"), (down, "down")):
                 p = getattr(layer, name); p.weight_loader(p, full[key][name].to(dev))
-        x = full["q"]["x"].to(dev)
-        # TP path: qkv (column) -> o on the q slice (row + reduce) -> gate_up (column) -> down on gate slice (row)
-        y_qkv, _ = qkv(x)
-        qw = heads * head // world
-        h, _ = o(y_qkv[:, :qw].contiguous())
-        y_gu, _ = gu(h)
-        iw = inter // world
-        out, _ = down(y_gu[:, :iw].contiguous())
-        torch.cuda.synchronize()
+        lin64 = lambda key, xin: O.linear_fp32(xin.cpu(), full[key]["codes"], full[key]["codebooks"],   # noqa: E731
+                                               full[key]["scales"], full[key]["partition_sizes"], None)
+        norm_w = (torch.rand(hidden, generator=torch.Generator().manual_seed(7)) + 0.5).to(dt)
+        qw, kvw, iw = heads * head // world, max(1, kv_heads // world) * head, inter // world
+        for t in (1, 4, 16):
+            x = full["q"]["x"][:t].to(dev)
+            res = full["o"]["x"][:t, :hidden].to(dev)
+            tag = f" {b}x{d}x{m} t={t}"
+            # column-parallel qkv: this rank's q rows (kv heads are divided or replicated, checked in the gloo tests)
+            y_qkv, _ = qkv(x)
+            report("qkv(q)", y_qkv[:, :qw], lin64("q", x)[:, rank * qw:(rank + 1) * qw], tag)
+            # row-parallel o_proj + all-reduce (fused in the GEMV epilogue for t <= 8, nbits <= 8)
+            attn = y_qkv[:, :qw].contiguous()
+            h, _ = o(attn)
+            h_ref = lin64("o", gather_cols(attn))
+            report("o_proj+allreduce", h, h_ref, tag)
+            if not same_on_all_ranks(h):
+                ok = False
+                print(f"[rank {rank}] o_proj result differs across ranks{tag}")
+            # the same with the residual add and the sum of squares in the epilogue, RMSNorm on gate_up's x load
+            z, _, ssq = o(attn, residual=res, want_ssq=True)
+            report("o_proj+allreduce+residual", z, h_ref + res.double().cpu(), tag)
+            y_gu, _ = gu(z, input_norm=(ssq, norm_w.to(dev), EPS))
+            xn_ref, _ = O.fused_add_rms_norm(z.cpu(), None, norm_w, EPS)
+            g_ref = torch.cat([lin64("gate", xn_ref)[:, rank * iw:(rank + 1) * iw],
+                               lin64("up", xn_ref)[:, rank * iw:(rank + 1) * iw]], -1)
+            report("rmsnorm+gate_up", y_gu, g_ref, tag)
+            # row-parallel down_proj with SiLU(gate) * up on its x load, + all-reduce + residual
+            out, _ = down(y_gu, input_act="silu_and_mul", residual=z)
+            act = O.silu_and_mul(y_gu.cpu())
+            out_ref = lin64("down", gather_cols(act.to(dev))) + z.double().cpu()
+            report("silu_mul+down_proj+allreduce+residual", out, out_ref, tag)
+            if not same_on_all_ranks(out):
+                ok = False
+                print(f"[rank {rank}] down_proj result differs across ranks{tag}")
+            # fused epilogue == separate launches (GEMV, one-shot all-reduce, add) up to fp16 rounding of the partials
+            os.environ["PQ_FUSED_ALLREDUCE"] = "0"
+            h_sep, _ = o(attn)
+            os.environ["PQ_FUSED_ALLREDUCE"] = "1"
+            rel = float((h.double() - h_sep.double()).pow(2).mean().sqrt() / h_sep.double().pow(2).mean().sqrt())
+            if not rel < 1e-3:
+                ok = False
+                print(f"[rank {rank}] fused vs separate all-reduce{tag}: {rel:.2e}")
+        # CUDA-graph replay of the fused chain (device-side epoch): 6 replays == eager
+        x1 = full["q"]["x"][:1].to(dev)
+        res1 = full["o"]["x"][:1, :hidden].to(dev)
 
-        # TP = 1 reference on this GPU from the same full tensors, through the same kernels
-        def lin(key, xin):
-            c = full[key]
-            return P.ops.pq_gemm(xin, c["codes"].to(dev), c["codebooks"].to(dev), c["scales"].to(dev),
-                                 c["partition_sizes"], None)
-        h1 = lin("o", lin("q", x))
-        out1 = lin("down", lin("gate", h1))
-        torch.cuda.synchronize()
-        scale = float(out1.float().abs().max())
-        err = float((out.float() - out1.float()).abs().max()) / scale
-        if not (err <= 5e-3):                       # also catches NaN
+        def chain():
+            yq, _ = qkv(x1)
+            zz, _, sq = o(yq[:, :qw].contiguous(), residual=res1, want_ssq=True)
+            yg, _ = gu(zz, input_norm=(sq, norm_w.to(dev), EPS))
+            oo, _ = down(yg, input_act="silu_and_mul", residual=zz)
+            return oo
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            eager = chain().clone()
+            chain()
+            st.synchronize()
+            dist.barrier()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=st):
+                outg = chain()
+            for _ in range(6):
+                gr.replay()
+            st.synchronize()
+        if not torch.equal(outg, eager):
             ok = False
-            print(f"[rank {rank}] TP stack {b}x{d}x{m}: rel err {err:.2e}")
-        elif rank == 0:
-            print(f"tp{world} stack {b}bit d{d} M{m}: max rel err vs tp1 = {err:.2e}")
+            print(f"[rank {rank}] graph replay of the fused chain != eager ({b}x{d}x{m})")
+        dist.barrier()
 
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)

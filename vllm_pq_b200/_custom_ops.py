@@ -16,6 +16,7 @@ captured in a CUDA graph (model_runner.py:1428-1562 in the reference).
 """
 from __future__ import annotations
 
+import ctypes
 from typing import List, Optional
 
 import torch
@@ -32,6 +33,10 @@ _LIBRARY.define("gemm_algo(Tensor input, Tensor codes, Tensor codebooks, Tensor 
 _LIBRARY.define("gemm_silu_mul(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes, Tensor? bias, int algo) -> Tensor")
 _LIBRARY.define("silu_and_mul(Tensor input) -> Tensor")
+_LIBRARY.define("gemm_fused(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
+                "int[] codebook_partition_sizes, Tensor? bias, Tensor? residual, Tensor? norm_ssq, "
+                "Tensor? norm_weight, float norm_eps, bool allreduce, bool silu_mul, bool want_ssq) -> (Tensor, Tensor)")
+_LIBRARY.define("fused_add_rms_norm(Tensor(a!) input, Tensor(b!)? residual, Tensor weight, float epsilon) -> ()")
 _LIBRARY.define("dequant(Tensor codes, Tensor codebooks, int[] codebook_partition_sizes) -> Tensor")
 _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes) -> Tensor")
@@ -162,6 +167,95 @@ def _gemm_impl(input, codes, codebooks, scales, parts, bias, algo, silu_mul=Fals
     return out.reshape(input.shape[:-1] + (n,))
 
 
+def gemm_fused_supported(t: int, n: int, k: int, d: int, nbits: int, m: int) -> bool:
+    """Does the decode table GEMV - the kernel that carries the fused epilogue - cover this problem?"""
+    return bool(_lib.load().pq_b200_gemm_fused_supported(t, n, k, d, nbits, m))
+
+
+def _gemm_fused_cuda(input, codes, codebooks, scales, parts, bias, residual, norm_ssq, norm_weight, norm_eps,
+                     allreduce, silu_mul, want_ssq):
+    """pq_b200_gemm_fused: the table GEMV with (norm on the x load | SiLU*mul on the x load), and in its
+    epilogue (all-reduce over the TP group,) (residual add,) (sum of squares per CTA).  SURVEY 8f N1."""
+    _require_cuda(input)
+    lib = _lib.load()
+    parts, n, g, m, d, nbits = _format(codes, codebooks, parts)
+    k = g * d
+    kx = 2 * k if silu_mul else k
+    dt = input.dtype
+    if input.shape[-1] != kx or dt not in _DTYPES or codebooks.dtype != dt or scales.dtype != dt:
+        raise RuntimeError("PQ: gemm_fused input/weight mismatch")
+    x = input.reshape(-1, kx)
+    if x.stride(-1) != 1 or (x.stride(0) * 2) % 16 or x.data_ptr() % 16:
+        x = x.contiguous()
+    t = x.shape[0]
+    if t < 1 or not gemm_fused_supported(t, n, k, d, nbits, m):
+        raise RuntimeError("PQ: gemm_fused needs the decode table GEMV (1..8 tokens, 8-bit codes); "
+                           "run the steps separately")
+    ep = _lib.Epilogue()
+    keep = []
+    if allreduce:
+        from . import distributed
+        comm = distributed.fused_allreduce_comm()
+        if comm is None or t * n > comm.LL_SLOT_ELEMS:
+            raise RuntimeError("PQ: gemm_fused(allreduce=True) without a peer-memory communicator")
+        comm.fill_epilogue(ep)
+    if residual is not None:
+        r2 = residual.reshape(-1, n)
+        if r2.dtype != dt or r2.shape[0] != t or r2.stride(-1) != 1:
+            raise RuntimeError("PQ: residual must be [T, N] of the input dtype")
+        ep.residual, ep.residual_stride = r2.data_ptr(), r2.stride(0)
+        keep.append(r2)
+    if norm_weight is not None:
+        if silu_mul or norm_ssq is None or norm_weight.dtype != dt or norm_weight.numel() != k:
+            raise RuntimeError("PQ: norm on load needs norm_ssq [T, slots] fp32 and a [K] weight")
+        nss = norm_ssq.reshape(t, -1)
+        if nss.dtype != torch.float32 or not nss.is_contiguous() or not norm_weight.is_contiguous():
+            raise RuntimeError("PQ: norm_ssq must be contiguous fp32")
+        ep.norm_ssq, ep.norm_weight = nss.data_ptr(), norm_weight.data_ptr()
+        ep.norm_slots, ep.norm_eps = nss.shape[1], float(norm_eps)
+        keep.append(nss)
+    ep.input_silu_mul = 1 if silu_mul else 0
+    arr, np_ = _lib.parts_array(parts)
+    out = torch.empty((t, n), dtype=dt, device=input.device)
+    with torch.cuda.device(input.device):
+        ws_bytes = lib.pq_b200_workspace_bytes(_lib.ALGO_GEMV_LUT_TMA, t, n, k, d, nbits, m, np_)
+        ws = _workspace(input.device, ws_bytes) if ws_bytes else None
+        ws_n = ws.numel() if ws is not None else 0
+        if want_ssq:
+            slots = lib.pq_b200_gemm_fused_slots(t, n, k, d, nbits, m, arr, np_, ws_n)
+            _lib.check(0 if slots > 0 else int(slots), "pq::gemm_fused (slots)")
+            ssq = torch.empty((t, slots), dtype=torch.float32, device=input.device)
+            ep.ssq_out, ep.ssq_slots = ssq.data_ptr(), slots
+        else:
+            ssq = torch.empty((0,), dtype=torch.float32, device=input.device)
+        rc = lib.pq_b200_gemm_fused(x.data_ptr(), x.stride(0), codes.data_ptr(), codebooks.data_ptr(),
+                                    scales.data_ptr(), _ptr(bias), out.data_ptr(), n, t, n, k, d, nbits, m,
+                                    arr, np_, _DTYPES[dt], _ptr(ws), ws_n,
+                                    torch.cuda.current_stream().cuda_stream, ctypes.byref(ep))
+    _lib.check(rc, "pq::gemm_fused")
+    del keep
+    return out.reshape(input.shape[:-1] + (n,)), ssq
+
+
+def _fused_add_rms_norm_cuda(input, residual, weight, epsilon):
+    _require_cuda(input)
+    h = input.shape[-1]
+    x = input.view(-1, h)
+    if input.dtype not in _DTYPES or weight.dtype != input.dtype or weight.numel() != h or x.stride(-1) != 1:
+        raise RuntimeError("PQ: fused_add_rms_norm takes fp16/bf16 [..., H] and a [H] weight")
+    r = None
+    if residual is not None:
+        r = residual.view(-1, h)
+        if r.dtype != input.dtype or r.shape != x.shape or r.stride(-1) != 1:
+            raise RuntimeError("PQ: residual must match input")
+    if x.shape[0]:
+        with torch.cuda.device(input.device):
+            rc = _lib.load().pq_b200_fused_add_rms_norm(x.data_ptr(), x.stride(0), _ptr(r), r.stride(0) if r is not None else 0,
+                                                        weight.data_ptr(), float(epsilon), x.shape[0], h,
+                                                        _DTYPES[input.dtype], torch.cuda.current_stream().cuda_stream)
+        _lib.check(rc, "pq::fused_add_rms_norm")
+
+
 def _gemm_cuda(input, codes, codebooks, scales, codebook_partition_sizes, bias):
     return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, _lib.ALGO_AUTO)
 
@@ -203,6 +297,8 @@ _LIBRARY.impl("gemm", _gemm_cuda, "CUDA")
 _LIBRARY.impl("gemm_algo", _gemm_algo_cuda, "CUDA")
 _LIBRARY.impl("gemm_silu_mul", _gemm_silu_mul_cuda, "CUDA")
 _LIBRARY.impl("silu_and_mul", _silu_and_mul_cuda, "CUDA")
+_LIBRARY.impl("gemm_fused", _gemm_fused_cuda, "CUDA")
+_LIBRARY.impl("fused_add_rms_norm", _fused_add_rms_norm_cuda, "CUDA")
 _LIBRARY.impl("dequant", _dequant_cuda, "CUDA")
 _LIBRARY.impl("dequant_scaled", _dequant_scaled_cuda, "CUDA")
 
@@ -238,6 +334,17 @@ torch.library.register_fake("pq::gemm_algo")(_gemm_algo_fake)
 torch.library.register_fake("pq::gemm_silu_mul")(_gemm_algo_fake)
 torch.library.register_fake("pq::silu_and_mul")(
     lambda input: torch.empty(input.shape[:-1] + (input.shape[-1] // 2,), dtype=input.dtype, device=input.device))
+def _gemm_fused_fake(input, codes, codebooks, scales, codebook_partition_sizes, bias, residual, norm_ssq,
+                     norm_weight, norm_eps, allreduce, silu_mul, want_ssq):
+    n = codes.size(0)
+    y = torch.empty(input.shape[:-1] + (n,), dtype=input.dtype, device=input.device)
+    t = y.numel() // n
+    # the slot count is the kernel's CTA count (pq_b200_gemm_fused_slots); a symbolic stand-in here
+    return y, torch.empty((t, 1) if want_ssq else (0,), dtype=torch.float32, device=input.device)
+
+
+torch.library.register_fake("pq::gemm_fused")(_gemm_fused_fake)
+torch.library.register_fake("pq::fused_add_rms_norm")(lambda input, residual, weight, epsilon: None)
 torch.library.register_fake("pq::dequant")(_dequant_fake)
 torch.library.register_fake("pq::dequant_scaled")(_dequant_scaled_fake)
 
@@ -262,6 +369,25 @@ def pq_gemm_silu_mul(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.
 def silu_and_mul(input: torch.Tensor) -> torch.Tensor:
     """SiluAndMul.forward_cuda (layers/activation.py:65-84) on this library's kernel."""
     return torch.ops.pq.silu_and_mul(input)
+
+
+def pq_gemm_fused(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor,
+                  codebook_partition_sizes: List[int], bias: Optional[torch.Tensor] = None, *,
+                  residual: Optional[torch.Tensor] = None, norm_ssq: Optional[torch.Tensor] = None,
+                  norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-6, allreduce: bool = False,
+                  silu_mul: bool = False, want_ssq: bool = False):
+    """(y, ssq): the decode table GEMV with its fused prologue / epilogue (include/pq_b200.h,
+    pq_b200_gemm_fused).  Replaces apply -> all_reduce -> fused_add_rms_norm -> ... of
+    linear.py:1209-1213 / llama.py:272-286 at decode."""
+    return torch.ops.pq.gemm_fused(input, codes, codebooks, scales, codebook_partition_sizes, bias, residual,
+                                   norm_ssq, norm_weight, norm_eps, allreduce, silu_mul, want_ssq)
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,
+                       epsilon: float) -> None:
+    """In place, as the reference's ops.fused_add_rms_norm / rms_norm (vllm/_custom_ops.py,
+    csrc/layernorm_kernels.cu:17-98): residual += input; input = RMSNorm(residual) * weight."""
+    torch.ops.pq.fused_add_rms_norm(input, residual, weight, epsilon)
 
 
 def pq_dequant(codes: torch.Tensor, codebooks: torch.Tensor,

@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, "libpq_b200.so")
 PQ_F16, PQ_BF16 = 0, 1
 ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC, ALGO_GEMM_MMA, ALGO_GEMV_LUT_TMA = 0, 1, 2, 3, 4, 5
 ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc", 4: "gemm_mma", 5: "gemv_lut_tma"}
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_PARTS = 8
 AR_FLAG_BYTES = 4096
 AR_MAX_WORLD = 8
@@ -24,6 +24,17 @@ AR_MAX_WORLD = 8
 # every symbol include/pq_b200.h declares: (restype, argtypes)
 _I64P = ctypes.POINTER(c_int64)
 _VPP = ctypes.POINTER(c_void_p)
+
+
+class Epilogue(ctypes.Structure):
+    """pq_b200_epilogue_t (include/pq_b200.h): extras of pq_b200_gemm_fused."""
+    _fields_ = [("ar_world", ctypes.c_int32), ("ar_rank", ctypes.c_int32), ("ar_peer", _VPP),
+                ("ar_state", c_void_p), ("ar_slot_elems", c_int64), ("residual", c_void_p),
+                ("residual_stride", c_int64), ("ssq_out", c_void_p), ("ssq_slots", c_int64),
+                ("norm_ssq", c_void_p), ("norm_weight", c_void_p), ("norm_slots", ctypes.c_int32),
+                ("norm_eps", ctypes.c_float), ("input_silu_mul", ctypes.c_int32)]
+
+
 SIGNATURES = {
     "pq_b200_abi_version": (c_int, []),
     "pq_b200_set_pdl": (None, [c_int]),
@@ -46,6 +57,13 @@ SIGNATURES = {
                                       c_int, c_int, c_void_p, c_int64, c_void_p]),
     "pq_b200_gemm_silu_mul_workspace_bytes": (c_int64, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int,
                                                         c_int]),
+    "pq_b200_gemm_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                   c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
+                                   c_int, c_void_p, c_int64, c_void_p, ctypes.POINTER(Epilogue)]),
+    "pq_b200_gemm_fused_supported": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int]),
+    "pq_b200_gemm_fused_slots": (c_int64, [c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int, c_int64]),
+    "pq_b200_fused_add_rms_norm": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, ctypes.c_float,
+                                           c_int64, c_int64, c_int, c_void_p]),
     "pq_b200_silu_and_mul": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int64, c_int, c_void_p]),
     "pq_b200_algo_supported": (c_int, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_pick_algo": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int]),

@@ -25,6 +25,7 @@ int silu_and_mul_dispatch(const void*, int64_t, void*, int64_t, int64_t, int64_t
 int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
 bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 bool gemv_lut2_preferred(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
+bool gemv_lut2_fused_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int gemm_tc_dispatch(const void*, int64_t, const void*, const void*, const void*, const void*,
                      void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
                      int, int, void*, int64_t, cudaStream_t);
@@ -273,15 +274,20 @@ int pq_b200_gemm_fused(const void* x, int64_t x_stride, const void* codes, const
   const int xact = (ep && ep->input_silu_mul) ? 1 : 0;
   if (t <= 0 || t > INT32_MAX || x_stride < (xact ? 2 * k : k) || y_stride < n) return PQ_ERR_SHAPE;
   if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
-  if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  if (!pq::gemv_lut2_fused_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
   return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
                                 part_sizes, n_parts, dtype, workspace, workspace_bytes, (cudaStream_t)stream, xact, ep);
+}
+
+int pq_b200_gemm_fused_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  if (t < 1 || n < 1 || k < 1 || d < 1 || k % d || m < 1) return 0;
+  return pq::gemv_lut2_fused_supported(t, n, k, d, nbits, m) ? 1 : 0;
 }
 
 int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, int nbits, int m,
                                  const int64_t* part_sizes, int n_parts, int64_t workspace_bytes) {
   if (check_format(n, k, d, nbits, m, part_sizes, n_parts, PQ_F16)) return PQ_ERR_SHAPE;
-  if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  if (!pq::gemv_lut2_fused_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
   return pq::gemv_lut2_grid_x(t, n, k, d, nbits, m, part_sizes, n_parts, workspace_bytes);
 }
 

@@ -84,6 +84,7 @@ struct Lut2Args {
   int trace_mask;         // which trace slots stamp (a %globaltimer read is slow: few stamps perturb less)
   // ---- fused epilogue of the row-parallel layers: all-reduce over NVLink peer memory,
   // residual add, sum of squares for the RMSNorm that follows ----
+  int ep_flags;           // 1: all-reduce (ar_world > 1), 2: residual, 4: ssq - 0 on the plain path
   int ar_world, ar_rank;  // ar_world > 1: y = sum over ranks of this rank's scaled partial rows
   unsigned long long* ar_peer[PQ_AR_MAX_WORLD];   // every rank's receive buffer: [2][world][ar_slot] packets
   unsigned int* ar_state; // this rank's {epoch counter, CTA ticket}
@@ -119,6 +120,7 @@ __device__ __forceinline__ float l2_allreduce_row(const Lut2Args& a, int tok, in
   const size_t idx = (size_t)tok * a.N + row;
   const size_t par = (size_t)(epoch & 1u) * a.ar_world;
   const unsigned long long pkt = ((unsigned long long)epoch << 32) | __float_as_uint(v);
+#pragma unroll 1
   for (int p = 1; p < a.ar_world; ++p) {
     int peer = a.ar_rank + p;
     if (peer >= a.ar_world) peer -= a.ar_world;
@@ -126,6 +128,7 @@ __device__ __forceinline__ float l2_allreduce_row(const Lut2Args& a, int tok, in
   }
   const unsigned long long* mine = a.ar_peer[a.ar_rank] + par * a.ar_slot + idx;
   float tot = 0.f;
+#pragma unroll 1
   for (int r = 0; r < a.ar_world; ++r) {
     float vr = v;
     if (r != a.ar_rank) {
@@ -343,7 +346,11 @@ __device__ __forceinline__ void l2_lookup16(float (&acc)[4], uint32_t lut_base, 
 // 96-register budget, and any extra live value in the kernel makes ptxas rematerialise the column
 // constants inside it (measured: 10 % slower on the large layers, profiles/r1_28).
 template <int CW, int COPY> constexpr int l2_threads() { return CW * 32 + 32 * (COPY ? kL2ProdWarps : 1); }
-template <typename T, int D, bool MASK, bool COPY, int CW>
+// FUSED: the instantiation that carries the fused prologue / epilogue (RMSNorm on the x load, all-reduce,
+// residual add, sums of squares).  A template parameter, not run-time flags: with run-time flags
+// alone the plain launch measured 0.3 us slower (profiles/r2_12_ab.txt) - set-up code of the fused
+// steps hoisted onto the latency-critical path after the dependency wait and before the stores.
+template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED>
 __global__ void __launch_bounds__(l2_threads<CW, COPY>(), CW <= 8 ? 2 : 1)
 pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
   constexpr int kL2ConsWarps = CW;
@@ -517,6 +524,10 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
 #pragma unroll
     for (int f = 0; f < XF; ++f) asm volatile("" : "+r"(xoff[f]));
     asm volatile("" : "+r"(lut_base), "+r"(emask4), "+r"(recv_addr), "+r"(xstep), "+r"(perm), "+l"(xg), "+l"(xs_mine));
+    // what the few instructions right after the wait need to know, in ONE register read before it
+    int post = a.xact == 1 ? 4 : 0;
+    if constexpr (FUSED) post |= (a.ar_world > 1 && tid == 0 ? 1 : 0) | (a.xact == 2 ? 2 : 0);
+    asm volatile("" : "+r"(post));
 
     // codes of one item (row iteration `it` of a tile) -> registers; the stage is released at once
     int stage = 0, round = 0;
@@ -563,12 +574,12 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     // fused all-reduce: this launch's epoch.  The counter is advanced by the last CTA of the previous
     // fused launch, which has completed by now; parked in shared memory, not in a register that
     // would live across the lookup loop.
-    if (a.ar_world > 1 && tid == 0)
+    if (FUSED && (post & 1))
       *epoch_smem = *reinterpret_cast<volatile unsigned int*>(a.ar_state) + 1u;
     // RMSNorm on the x load: rstd from the producer's per-CTA sums of squares, added in a fixed
     // order by every warp on its own (no barrier; layernorm_kernels.cu:82-88)
     float rstd = 1.f;
-    if (a.xact == 2) {
+    if (FUSED && (post & 2)) {
       float ss = 0.f;
       for (int j = lane; j < a.nrm_slots; j += 32) ss += __ldcg(a.nrm_ssq + (size_t)tok * a.nrm_slots + j);
       rstd = rsqrtf(warp_sum(ss) / (float)a.K + a.nrm_eps);
@@ -584,9 +595,9 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
           if (xoff[f] >= 0 && elem < a.K) {
             v = __ldg(reinterpret_cast<const uint32_t*>(xg + elem));
             // x is [T, 2K] = (gate | up): SiLU(gate) * up on the way in (llama.py:89-93)
-            if (a.xact == 1) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
+            if (post & 4) v = silu_mul_pair<T>(v, __ldg(reinterpret_cast<const uint32_t*>(xg + a.K + elem)));
             // x is the residual stream z: RMSNorm(z) * w on the way in (layernorm_kernels.cu:91-97)
-            else if (a.xact == 2)
+            else if (FUSED && (post & 2))
               v = rms_norm_pair<T>(v, rstd, __ldg(reinterpret_cast<const uint32_t*>(reinterpret_cast<const T*>(a.nrm_w) + elem)));
           }
           xs_mine[s * XW + f * kL2Cons] = v;
@@ -646,15 +657,20 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   }
   l2_trace(a, 6);
   // One finished row: (all-reduce over the TP ranks,) one rounding of y, (residual add,) store.
-  const uint32_t epoch = a.ar_world > 1 ? *epoch_smem : 0u;
+  // (the plain launch pays one flag test here: the fused steps sit behind it, their loops not unrolled,
+  // so that nothing of theirs is hoisted onto the plain path - measured 0.3 us per launch when it was)
+  const int efl = FUSED ? a.ep_flags : 0;          // 1: all-reduce, 2: residual, 4: ssq
+  const uint32_t epoch = (efl & 1) ? *epoch_smem : 0u;
   float ssq_local = 0.f;
   auto store_row = [&](int row, float v) {
+    T* yp = reinterpret_cast<T*>(a.y) + (size_t)tok * a.y_stride + row;
+    if (efl == 0) { *yp = Traits<T>::from_f(v); return; }
     float res = 0.f;
-    if (a.resid) res = Traits<T>::to_f(reinterpret_cast<const T*>(a.resid)[(size_t)tok * a.resid_stride + row]);
-    if (a.ar_world > 1) v = l2_allreduce_row(a, tok, row, v, epoch);
+    if (efl & 2) res = Traits<T>::to_f(reinterpret_cast<const T*>(a.resid)[(size_t)tok * a.resid_stride + row]);
+    if (efl & 1) v = l2_allreduce_row(a, tok, row, v, epoch);
     T out = Traits<T>::from_f(v);
-    if (a.resid) out = Traits<T>::from_f(Traits<T>::to_f(out) + res);   // z = x + residual in T (layernorm_kernels.cu:75-80)
-    reinterpret_cast<T*>(a.y)[(size_t)tok * a.y_stride + row] = out;
+    if (efl & 2) out = Traits<T>::from_f(Traits<T>::to_f(out) + res);   // z = x + residual in T (layernorm_kernels.cu:75-80)
+    *yp = out;
     const float zf = Traits<T>::to_f(out);
     ssq_local = fmaf(zf, zf, ssq_local);
   };
@@ -703,8 +719,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     }
   }
   // ---- this CTA's share of sum(y^2) for the RMSNorm the consumer applies on its x load: warps in
-  // order, then thread 0 in warp order - a fixed order (CTAs that stored nothing write 0) ----
-  if (a.ssq != nullptr) {
+  // order, then thread 0 in warp order - a fixed order ----
+  if ((efl & 4) && (a.KG == 1 || *reinterpret_cast<int*>(bars + 2 * kL2MaxStages))) {
     __syncthreads();                               // everyone is done reading rowsum / recv
     const float w = warp_sum(ssq_local);
     if (lane == 0) rowsum[warp] = w;
@@ -712,11 +728,13 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     if (tid == 0) {
       float tot = 0.f;
       for (int i = 0; i < l2_threads<CW, COPY>() / 32; ++i) tot += rowsum[i];
-      a.ssq[(size_t)tok * gridDim.x + blockIdx.x] = tot;
+      // slot = (row block, rank): with K groups only the CTA that finished the rows writes, so
+      // every slot is written exactly once per launch, whichever K group came last
+      a.ssq[(size_t)tok * (gridDim.x / a.KG) + block * a.CS + rank] = tot;
     }
   }
   // ---- fused all-reduce: the last CTA of the launch advances this rank's epoch ----
-  if (a.ar_world > 1) {
+  if (efl & 1) {
     __syncthreads();
     if (tid == 0) {
       const unsigned int n_cta = gridDim.x * gridDim.y;
@@ -751,7 +769,7 @@ static int lut2_log2(int cs) { return cs == 1 ? 0 : cs == 2 ? 1 : cs == 4 ? 2 : 
 
 template <int CW>
 static int lut2_query_clusters(int cs, int smem) {
-  auto kern = pq_gemv_lut2_kernel<__half, 8, false, false, CW>;
+  auto kern = pq_gemv_lut2_kernel<__half, 8, false, false, CW, false>;
   int n = -1;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024) != cudaSuccess) return -1;
   if (cs > 8 && cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) return -1;
@@ -897,13 +915,13 @@ int gemv_lut2_debug_plan(int64_t t, int64_t n, int64_t k, int d, int nbits, int 
   return PQ_OK;
 }
 
-// gridDim.x of the launch (= floats per token of the fused epilogue's ssq output), or a negative error
+// CTAs that finish rows (= floats per token of the fused epilogue's ssq output), or a negative error
 int64_t gemv_lut2_grid_x(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
                          int n_parts, int64_t workspace_bytes) {
   Lut2Plan pl;
   const bool have_ws = workspace_bytes >= kL2TicketBytes + (int64_t)kL2MaxKG * t * n * 4;
   if (!lut2_plan(pl, t, n, k, d, nbits, m, part_sizes, n_parts, have_ws)) return PQ_ERR_UNSUPPORTED;
-  return lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.kg * pl.cs;
+  return lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.cs;
 }
 
 // Upper bound for every plan (the plan may depend on the partition sizes): tickets + KG partials.
@@ -921,6 +939,11 @@ bool gemv_lut2_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int 
   if (gp > (int64_t)1 << 30 || n > (int64_t)1 << 30) return false;
   Lut2Plan pl;
   return lut2_plan(pl, t, n, k, d, nbits, m, nullptr, PQ_MAX_PARTS);
+}
+
+// The fused prologue / epilogue is instantiated for 8-bit codes only.
+bool gemv_lut2_fused_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m) {
+  return nbits == 8 && gemv_lut2_supported(t, n, k, d, nbits, m);
 }
 
 // PQ_ALGO_AUTO heuristic: tiny problems are better served by the direct kernel.
@@ -961,9 +984,9 @@ static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-template <typename T, int D, bool MASK, bool COPY, int CW>
+template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED>
 static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY, CW>;
+  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY, CW, FUSED>;
   static bool attr_set[64] = {};                   // per instantiation, per device
   int dev = 0;
   cudaGetDevice(&dev);
@@ -994,11 +1017,20 @@ static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl
 
 template <typename T, int D, bool MASK>
 static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
+  if constexpr (!MASK) {                           // fused steps: 8-bit codes only (gemv_lut2_fused_supported)
+    if (a.ep_flags || a.xact == 2) {
+      if (pl.cw == 8)
+        return a.copy_w ? launch_lut2_c<T, D, false, true, 8, true>(map, a, pl, stream)
+                        : launch_lut2_c<T, D, false, false, 8, true>(map, a, pl, stream);
+      return a.copy_w ? launch_lut2_c<T, D, false, true, 16, true>(map, a, pl, stream)
+                      : launch_lut2_c<T, D, false, false, 16, true>(map, a, pl, stream);
+    }
+  }
   if (pl.cw == 8)
-    return a.copy_w ? launch_lut2_c<T, D, MASK, true, 8>(map, a, pl, stream)
-                    : launch_lut2_c<T, D, MASK, false, 8>(map, a, pl, stream);
-  return a.copy_w ? launch_lut2_c<T, D, MASK, true, 16>(map, a, pl, stream)
-                  : launch_lut2_c<T, D, MASK, false, 16>(map, a, pl, stream);
+    return a.copy_w ? launch_lut2_c<T, D, MASK, true, 8, false>(map, a, pl, stream)
+                    : launch_lut2_c<T, D, MASK, false, 8, false>(map, a, pl, stream);
+  return a.copy_w ? launch_lut2_c<T, D, MASK, true, 16, false>(map, a, pl, stream)
+                  : launch_lut2_c<T, D, MASK, false, 16, false>(map, a, pl, stream);
 }
 
 template <typename T>
@@ -1050,7 +1082,8 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.smem_cb = pl.smem_cb; a.smem_x = pl.smem_x; a.mask = nbits < 8 ? 1 : 0;
   a.trace = g_lut_trace; a.xact = xact;
   if (ep != nullptr) {
-    const int64_t grid_x = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.kg * pl.cs;
+    if (nbits != 8) return PQ_ERR_UNSUPPORTED;
+    const int64_t ssq_slots = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster) * pl.cs;
     if (ep->ar_world > 1) {
       if (ep->ar_world > PQ_AR_MAX_WORLD || ep->ar_rank < 0 || ep->ar_rank >= ep->ar_world) return PQ_ERR_SHAPE;
       if (!ep->ar_peer || !ep->ar_state) return PQ_ERR_NULL;
@@ -1064,7 +1097,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
     }
     if (ep->residual) { a.resid = ep->residual; a.resid_stride = ep->residual_stride; }
     if (ep->ssq_out) {
-      if (ep->ssq_slots != grid_x) return PQ_ERR_WORKSPACE;       // pq_b200_gemm_fused_slots() of this problem
+      if (ep->ssq_slots != ssq_slots) return PQ_ERR_WORKSPACE;       // pq_b200_gemm_fused_slots() of this problem
       a.ssq = ep->ssq_out;
     }
     if (ep->norm_weight) {
@@ -1077,6 +1110,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   static const int early_ld = lut2_env("PQ_LUT2_EARLY_LD", 0);
   a.early_ld = early_ld;
   a.trace_mask = lut2_env("PQ_LUT2_TRACE_MASK", 0xffff);
+  a.ep_flags = (a.ar_world > 1 ? 1 : 0) | (a.resid ? 2 : 0) | (a.ssq ? 4 : 0);
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
   if (rc) return rc;
   CUtensorMap map;

@@ -103,6 +103,14 @@ def oneshot_enabled() -> bool:
     return _ONESHOT is not None
 
 
+def fused_allreduce_comm() -> Optional["OneShotAllReduce"]:
+    """The peer-memory communicator the fused GEMV + all-reduce epilogue uses, or None (TP = 1, no
+    peer access, or PQ_FUSED_ALLREDUCE=0)."""
+    if _ONESHOT is None or os.environ.get("PQ_FUSED_ALLREDUCE", "1") == "0":
+        return None
+    return _ONESHOT
+
+
 def tensor_model_parallel_all_reduce(input_: torch.Tensor) -> torch.Tensor:
     """All-reduce SUM across the TP group; passthrough at world size 1
     (parallel_state.py:303-304)."""
@@ -132,6 +140,10 @@ class OneShotAllReduce:
     Eligibility follows custom_all_reduce.py:247-260: fp16/bf16, 16-byte multiple,
     at most ``max_bytes``; world size 2/4/8 on one NVSwitch node."""
 
+    # fused GEMV + all-reduce (csrc/pq_gemv_lut2.cu): receive buffer of {fp32, epoch} packets,
+    # [2 parities][world][LL_SLOT_ELEMS]; 8 tokens (the table GEMV's limit) x 16384 outputs
+    LL_SLOT_ELEMS = 8 * 16384
+
     def __init__(self, group: dist.ProcessGroup, max_bytes: int):
         from . import _lib
         self._libmod = _lib
@@ -143,15 +155,20 @@ class OneShotAllReduce:
         self._opened: List[int] = []
         # two staging slots (alternating by the device-side epoch parity) so that a fast
         # rank's next push cannot overwrite data a slow rank is still summing
-        self.data = self.flags = None
+        self.data = self.flags = self.ll_data = self.ll_state = None
         mine = None
         try:
             self.data = self._malloc(2 * self.world * self.max_bytes)
             self.flags = self._malloc(_lib.AR_FLAG_BYTES)
+            ll_bytes = 2 * self.world * self.LL_SLOT_ELEMS * 8
+            self.ll_data = self._malloc(ll_bytes)
+            self.ll_state = self._malloc(256)        # {epoch, ticket}: local only, never mapped by peers
             stream = torch.cuda.current_stream().cuda_stream
             _lib.check(self.lib.pq_b200_memset_async(self.flags, 0, _lib.AR_FLAG_BYTES, stream), "memset")
+            _lib.check(self.lib.pq_b200_memset_async(self.ll_data, 0, ll_bytes, stream), "memset")
+            _lib.check(self.lib.pq_b200_memset_async(self.ll_state, 0, 256, stream), "memset")
             torch.cuda.synchronize()
-            mine = (self._handle(self.data), self._handle(self.flags))
+            mine = (self._handle(self.data), self._handle(self.flags), self._handle(self.ll_data))
         except Exception as exc:                       # noqa: BLE001 - the collective below must still run
             mine = None
             local_error = exc
@@ -163,12 +180,14 @@ class OneShotAllReduce:
             raise RuntimeError("a peer could not allocate its staging buffers")
         self.peer_data = (ctypes.c_void_p * self.world)()
         self.peer_flags = (ctypes.c_void_p * self.world)()
-        for r, (hd, hf) in enumerate(handles):
+        self.peer_ll = (ctypes.c_void_p * self.world)()
+        for r, (hd, hf, hl) in enumerate(handles):
             if r == self.rank:
-                self.peer_data[r], self.peer_flags[r] = self.data, self.flags
+                self.peer_data[r], self.peer_flags[r], self.peer_ll[r] = self.data, self.flags, self.ll_data
             else:
                 self.peer_data[r] = self._open(hd)
                 self.peer_flags[r] = self._open(hf)
+                self.peer_ll[r] = self._open(hl)
         # no barrier here: the caller (_setup_oneshot) ends with a group-wide agreement, which also
         # orders every rank's memset of its flags before any peer's first kernel
 
@@ -188,6 +207,13 @@ class OneShotAllReduce:
         self._libmod.check(self.lib.pq_b200_ipc_open_handle(buf, ctypes.byref(p)), "ipc_open_handle")
         self._opened.append(p.value)
         return p.value
+
+    def fill_epilogue(self, ep) -> None:
+        """all-reduce fields of a _lib.Epilogue (pq_b200_epilogue_t)."""
+        ep.ar_world, ep.ar_rank = self.world, self.rank
+        ep.ar_peer = ctypes.cast(self.peer_ll, ctypes.POINTER(ctypes.c_void_p))
+        ep.ar_state = self.ll_state
+        ep.ar_slot_elems = self.LL_SLOT_ELEMS
 
     def eligible(self, t: torch.Tensor) -> bool:
         nbytes = t.numel() * t.element_size()
@@ -209,7 +235,7 @@ class OneShotAllReduce:
             torch.cuda.synchronize()
             for p in self._opened:
                 self.lib.pq_b200_ipc_close_handle(p)
-            for p in (self.data, self.flags):
+            for p in (self.data, self.flags, self.ll_data, self.ll_state):
                 if p:
                     self.lib.pq_b200_free(p)
         except Exception:

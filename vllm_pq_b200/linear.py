@@ -123,9 +123,16 @@ class ColumnParallelLinear(LinearBase):
             loaded_weight = loaded_weight.narrow(output_dim, get_tensor_model_parallel_rank() * shard, shard)
         _copy(param.data, loaded_weight)
 
-    def forward(self, input_) -> Union[torch.Tensor, Tuple[torch.Tensor, Optional[Parameter]]]:
+    def forward(self, input_, input_norm=None) -> Union[torch.Tensor, Tuple[torch.Tensor, Optional[Parameter]]]:
+        """`input_norm=(ssq, weight, eps)`: `input_` is the residual stream and the layer's input is
+        RMSNorm(input_) * weight (llama.py:272-283) - taken on the kernel's x load at decode, with the
+        sum of squares `ssq` handed over by the row-parallel layer that produced `input_`
+        (`want_ssq=True`; None: computed by a norm launch).  SURVEY.md 8f, N1."""
         bias = self.bias if not self.skip_bias_add else None
-        output = self.quant_method.apply(self, input_, bias)          # no collective (linear.py:425)
+        if input_norm is not None:
+            output, _ = self.quant_method.apply_fused(self, input_, bias, norm=input_norm)
+        else:
+            output = self.quant_method.apply(self, input_, bias)      # no collective (linear.py:425)
         if self.gather_output:
             output = tensor_model_parallel_all_gather(output)
         return self._ret(output, self.bias if self.skip_bias_add else None)
@@ -274,10 +281,16 @@ class RowParallelLinear(LinearBase):
             loaded_weight = loaded_weight.narrow(input_dim, self.tp_rank * shard, shard)
         _copy(param.data, loaded_weight)
 
-    def forward(self, input_, input_act: Optional[str] = None):
+    def forward(self, input_, input_act: Optional[str] = None, residual: Optional[torch.Tensor] = None,
+                want_ssq: bool = False):
         """`input_act="silu_and_mul"`: `input_` is this rank's (gate | up) out of the merged
         column-parallel layer and the layer's input is SiLU(gate) * up (llama.py:89-93) - taken on
-        the kernel's x load instead of by an activation launch in between."""
+        the kernel's x load instead of by an activation launch in between.
+        `residual`: the output is all_reduce(y) + residual, i.e. the new residual stream of
+        llama.py:276-283; `want_ssq=True` also returns its per-CTA sums of squares for the RMSNorm
+        the next column-parallel layer applies on its x load (`input_norm`).  At decode the
+        all-reduce, the add and the squares are the table GEMV's epilogue (SURVEY.md 8f, N1);
+        otherwise they run as separate launches."""
         if input_act not in (None, "silu_and_mul"):
             raise ValueError(f"unknown input activation {input_act!r}")
         if self.input_is_parallel:
@@ -289,12 +302,22 @@ class RowParallelLinear(LinearBase):
             input_parallel = input_.narrow(-1, self.tp_rank * chunk, chunk).contiguous()
         # bias enters the sum exactly once (linear.py:1206-1208)
         bias_ = None if (self.tp_rank > 0 or self.skip_bias_add) else self.bias
-        if input_act is None:
-            output_parallel = self.quant_method.apply(self, input_parallel, bias=bias_)
+        reduce_ = self.reduce_results and self.tp_size > 1
+        ssq = None
+        if (reduce_ or residual is not None or want_ssq) and hasattr(self.quant_method, "apply_fused"):
+            output, ssq = self.quant_method.apply_fused(self, input_parallel, bias_, residual=residual,
+                                                        allreduce=reduce_, silu_mul=input_act is not None,
+                                                        want_ssq=want_ssq)
         else:
-            output_parallel = self.quant_method.apply_silu_mul(self, input_parallel, bias=bias_)
-        if self.reduce_results and self.tp_size > 1:
-            output = tensor_model_parallel_all_reduce(output_parallel)
-        else:
-            output = output_parallel
-        return self._ret(output, self.bias if self.skip_bias_add else None)
+            if input_act is None:
+                output = self.quant_method.apply(self, input_parallel, bias=bias_)
+            else:
+                output = self.quant_method.apply_silu_mul(self, input_parallel, bias=bias_)
+            if reduce_:
+                output = tensor_model_parallel_all_reduce(output)
+            if residual is not None:
+                output = output + residual
+        ret = self._ret(output, self.bias if self.skip_bias_add else None)
+        if want_ssq:
+            return (ret + (ssq,)) if isinstance(ret, tuple) else (ret, ssq)
+        return ret

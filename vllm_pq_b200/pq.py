@@ -174,6 +174,52 @@ class PQLinearMethodBody:
         return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales,
                                     list(getattr(codebooks, "output_partition_sizes", [])), bias)
 
+    def apply_fused(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
+                    residual: Optional[torch.Tensor] = None, norm=None, allreduce: bool = False,
+                    silu_mul: bool = False, want_ssq: bool = False):
+        """(z, ssq) with  z = all_reduce(apply(act(norm(x)))) + residual  - the chain the reference runs
+        as separate launches around a row-parallel layer (linear.py:1209-1213, llama.py:272-286,
+        layernorm_kernels.cu:52-98).  ``norm`` = (ssq or None, weight, eps): RMSNorm of x, its sum of
+        squares coming from the producer's ``ssq`` ([T, slots] fp32) when there is one.  At decode
+        (1..8 tokens, nbits <= 8) everything rides on the table GEMV's x load and epilogue; otherwise
+        the same steps run as separate launches with the same roundings."""
+        from . import distributed as D
+        codes, codebooks = layer.codes, layer.codebooks
+        parts = list(getattr(codebooks, "output_partition_sizes", []))
+        n, g, m = codes.shape
+        d, nbits = codebooks.shape[3], codebooks.shape[1].bit_length() - 1
+        t = x.numel() // x.shape[-1] if x.shape[-1] else 0
+        comm = D.fused_allreduce_comm() if allreduce else None
+        fused = (x.is_cuda and t >= 1 and ops.gemm_fused_supported(t, n, g * d, d, nbits, m)
+                 and (not allreduce or (comm is not None and t * n <= comm.LL_SLOT_ELEMS))
+                 and not (norm is not None and silu_mul))
+        if norm is not None and (not fused or norm[0] is None):
+            x = self._rms_norm(x, *norm)
+            norm = None
+        if fused:
+            ns, nw, ne = norm if norm is not None else (None, None, 1e-6)
+            y, ssq = ops.pq_gemm_fused(x, codes, codebooks, layer.scales, parts, bias, residual=residual,
+                                       norm_ssq=ns, norm_weight=nw, norm_eps=ne, allreduce=allreduce,
+                                       silu_mul=silu_mul, want_ssq=want_ssq)
+            return y, (ssq if want_ssq else None)
+        y = (ops.pq_gemm_silu_mul if silu_mul else ops.pq_gemm)(x, codes, codebooks, layer.scales, parts, bias)
+        if allreduce:
+            y = D.tensor_model_parallel_all_reduce(y)
+        if residual is not None:
+            y = y + residual.reshape(y.shape)
+        ssq = y.float().pow(2).sum(-1).reshape(-1, 1) if want_ssq else None
+        return y, ssq
+
+    @staticmethod
+    def _rms_norm(x: torch.Tensor, ssq: Optional[torch.Tensor], weight: torch.Tensor, eps: float) -> torch.Tensor:
+        """RMSNorm(x) * weight as its own step; roundings of layernorm_kernels.cu:91-97."""
+        if ssq is None:
+            out = x.clone()
+            ops.fused_add_rms_norm(out, None, weight, eps)
+            return out
+        rstd = torch.rsqrt(ssq.reshape(-1, ssq.shape[-1]).sum(-1, keepdim=True) / x.shape[-1] + eps)
+        return ((x.reshape(-1, x.shape[-1]).float() * rstd).to(x.dtype) * weight).reshape(x.shape)
+
     def dequantize(self, layer: torch.nn.Module, scaled: bool = True) -> torch.Tensor:
         """Dense [N, K] weight (aqlm.py:37-74); bit-exact with the reference."""
         codebooks = layer.codebooks
