@@ -123,6 +123,7 @@ def main():
         lin64 = lambda key, xin: O.linear_fp32(xin.cpu(), full[key]["codes"], full[key]["codebooks"],   # noqa: E731
                                                full[key]["scales"], full[key]["partition_sizes"], None)
         norm_w = (torch.rand(hidden, generator=torch.Generator().manual_seed(7)) + 0.5).to(dt)
+        norm_w_dev = norm_w.to(dev)
         qw, kvw, iw = heads * head // world, max(1, kv_heads // world) * head, inter // world
         for t in (1, 4, 16):
             x = full["q"]["x"][:t].to(dev)
@@ -142,7 +143,7 @@ def main():
             # the same with the residual add and the sum of squares in the epilogue, RMSNorm on gate_up's x load
             z, _, ssq = o(attn, residual=res, want_ssq=True)
             report("o_proj+allreduce+residual", z, h_ref + res.double().cpu(), tag)
-            y_gu, _ = gu(z, input_norm=(ssq, norm_w.to(dev), EPS))
+            y_gu, _ = gu(z, input_norm=(ssq, norm_w_dev, EPS))
             xn_ref, _ = O.fused_add_rms_norm(z.cpu(), None, norm_w, EPS)
             g_ref = torch.cat([lin64("gate", xn_ref)[:, rank * iw:(rank + 1) * iw],
                                lin64("up", xn_ref)[:, rank * iw:(rank + 1) * iw]], -1)
@@ -170,7 +171,7 @@ def main():
         def chain():
             yq, _ = qkv(x1)
             zz, _, sq = o(yq[:, :qw].contiguous(), residual=res1, want_ssq=True)
-            yg, _ = gu(zz, input_norm=(sq, norm_w.to(dev), EPS))
+            yg, _ = gu(zz, input_norm=(sq, norm_w_dev, EPS))
             oo, _ = down(yg, input_act="silu_and_mul", residual=zz)
             return oo
         st = torch.cuda.Stream()
