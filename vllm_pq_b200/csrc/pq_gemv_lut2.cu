@@ -69,7 +69,8 @@ struct Lut2Args {
                           // down_proj) - the producer warp copies with cp.async of this width instead
   int n_tiles;            // ceil(Gp / 64)
   int S;                  // tiles per CTA = ceil(n_tiles / CS)
-  int CS;                 // cluster size
+  int CS;                 // cluster size (a power of two)
+  int cs_log2, m_log2;    // the prologue is on every layer's critical path: shifts, not divisions
   int rows_per_cluster;   // multiple of 64
   int KG;                 // clusters along K per row block (each owns CS * S consecutive tiles)
   float* ws_part;         // KG > 1: [T][KG][N] fp32 partial sums (workspace)
@@ -127,17 +128,22 @@ __device__ __forceinline__ float l2_allreduce_row(const Lut2Args& a, int tok, in
     l2_st_sys_u64(a.ar_peer[peer] + (par + a.ar_rank) * a.ar_slot + idx, pkt);
   }
   const unsigned long long* mine = a.ar_peer[a.ar_rank] + par * a.ar_slot + idx;
+  // all peers' packets are polled together: one L2 round trip per attempt, not one per peer
+  unsigned long long got[PQ_AR_MAX_WORLD];
+  bool all;
+  do {
+    all = true;
+#pragma unroll
+    for (int r = 0; r < PQ_AR_MAX_WORLD; ++r)
+      if (r < a.ar_world && r != a.ar_rank) got[r] = l2_ld_sys_u64(mine + (size_t)r * a.ar_slot);
+#pragma unroll
+    for (int r = 0; r < PQ_AR_MAX_WORLD; ++r)
+      if (r < a.ar_world && r != a.ar_rank) all = all && ((uint32_t)(got[r] >> 32) == epoch);
+  } while (!all);
   float tot = 0.f;
-#pragma unroll 1
-  for (int r = 0; r < a.ar_world; ++r) {
-    float vr = v;
-    if (r != a.ar_rank) {
-      unsigned long long got;
-      do { got = l2_ld_sys_u64(mine + (size_t)r * a.ar_slot); } while ((uint32_t)(got >> 32) != epoch);
-      vr = __uint_as_float((uint32_t)got);
-    }
-    tot += vr;
-  }
+#pragma unroll
+  for (int r = 0; r < PQ_AR_MAX_WORLD; ++r)
+    if (r < a.ar_world) tot += (r == a.ar_rank) ? v : __uint_as_float((uint32_t)got[r]);
   return tot;
 }
 
@@ -146,7 +152,7 @@ __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
   if (a.trace != nullptr && threadIdx.x == 0 && ((a.trace_mask >> slot) & 1)) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
+    a.trace[(((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
   }
 }
 
@@ -157,7 +163,7 @@ __device__ __forceinline__ void l2_trace_dep(const Lut2Args& a, int slot, const 
     const uint32_t dep = *p;
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) : "r"(dep));
-    a.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
+    a.trace[(((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * kL2TraceSlots + slot] = t;
   }
 }
 
@@ -237,13 +243,13 @@ template <int D> constexpr int l2_x_words() { return D == 16 ? 512 : 256; }
 // zero words of D = 4.  Computed before the dependency wait; after it each thread only adds the
 // tile step, loads 4 bytes and stores them.
 template <int D>
-__device__ __forceinline__ int l2_x_offset(int f, int tile, int M) {
-  const int gpt = kL2Tile / M;                     // x groups per tile
+__device__ __forceinline__ int l2_x_offset(int f, int tile, int m_log2) {
+  const int gpt = kL2Tile >> m_log2;               // x groups per tile
   const int half = f >> 8, r = f & 255, hb = r >> 7, jn = (r >> 5) & 3, ln = r & 31;
   const int g = ln >> 2, tq = ln & 3;
   const int pos = 16 * (g >> 1) + 4 * (hb + 2 * (g & 1)) + jn;
   if (D == 4 && tq >= 2) return -1;
-  return (tile * gpt + pos / M) * D + 2 * (tq + 4 * half);
+  return (tile * gpt + (pos >> m_log2)) * D + 2 * (tq + 4 * half);
 }
 
 // Half a table (the 32 positions with j & 1 == hb of one 64-position tile) on the tensor cores:
@@ -372,24 +378,24 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   if (a.early_ld) pdl_launch_dependents();
   const bool clustered = a.CS > 1;
   const int rank = clustered ? (int)l2_cluster_rank() : 0;
-  const int tok = blockIdx.y;
+  // grid = (CS * KG, row blocks, tokens): no division to find this CTA's place
+  const int tok = blockIdx.z;
   l2_trace(a, 0);
   // every CTA of the cluster has started once this barrier phase completes (waited for just before
   // the first distributed-shared-memory store, long after everyone arrived)
   if (clustered) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
-  const int cid = blockIdx.x / a.CS;               // cluster: (row block, K group)
-  const int block = cid / a.KG, kg = cid - block * a.KG;
+  const int block = blockIdx.y, kg = blockIdx.x >> a.cs_log2;   // cluster: (row block, K group)
   const int tile0 = kg * a.CS * a.S + rank;        // this CTA's tiles: tile0, tile0 + CS, ... (S of them)
   const RowBlock rb = locate_row_block(a.parts, block, a.rows_per_cluster);
   const int rows = rb.row1 - rb.row0;
   const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
   // tiles of this CTA that exist (the last K group may leave some ranks with none)
-  const int my_tiles = tile0 < a.n_tiles ? min(a.S, (a.n_tiles - tile0 + a.CS - 1) / a.CS) : 0;
+  const int my_tiles = tile0 < a.n_tiles ? min(a.S, (a.n_tiles - tile0 + a.CS - 1) >> a.cs_log2) : 0;
   const int total = my_tiles * n_iter;
 
   // the rows this CTA finishes: scale and bias are weights too - fetch them now (raw bits:
   // converting here would stall on the load)
-  const int chunk = (rows + a.CS - 1) / a.CS;
+  const int chunk = (rows + a.CS - 1) >> a.cs_log2;
   const int fin0 = rank * chunk, fin1 = min(rows, fin0 + chunk);
   unsigned short sc0_raw = 0, bi0_raw = 0;
   if (fin0 + tid < fin1) {
@@ -406,11 +412,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
 
-  if (tid == 0) {
-    for (int i = 0; i < a.stages; ++i) {
-      l2_mbar_init(full0 + 8 * i, COPY ? 32 * kL2ProdWarps : 1);
-      l2_mbar_init(empty0 + 8 * i, kL2ConsWarps);
-    }
+  if (tid < 2 * kL2MaxStages) {                    // one barrier per thread (all slots: no loop, no stage count)
+    l2_mbar_init(full0 + 8 * tid, tid < kL2MaxStages ? (COPY ? 32 * kL2ProdWarps : 1) : kL2ConsWarps);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -510,8 +513,8 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     constexpr int XF = XW > kL2Cons ? XW / kL2Cons : 1;      // fragment words per thread
     int xoff[XF];
 #pragma unroll
-    for (int f = 0; f < XF; ++f) xoff[f] = tid + f * kL2Cons < XW ? l2_x_offset<D>(tid + f * kL2Cons, tile0, a.M) : -1;
-    int xstep = a.CS * (kL2Tile / a.M) * D;        // elements between this CTA's consecutive tiles
+    for (int f = 0; f < XF; ++f) xoff[f] = tid + f * kL2Cons < XW ? l2_x_offset<D>(tid + f * kL2Cons, tile0, a.m_log2) : -1;
+    int xstep = a.CS * (kL2Tile >> a.m_log2) * D;  // elements between this CTA's consecutive tiles
     const T* xg = reinterpret_cast<const T*>(a.x) + (size_t)tok * a.x_stride;
     uint32_t* xs_mine = reinterpret_cast<uint32_t*>(xs) + tid;
     // all of the above is integer work on lane ids and launch constants: make sure it is done
@@ -695,7 +698,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     int* last_flag = reinterpret_cast<int*>(bars + 2 * kL2MaxStages);
     __threadfence();
     __syncthreads();
-    int* ticket = a.ws_tickets + ((size_t)tok * gridDim.x / (a.CS * a.KG) + block) * a.CS + rank;
+    int* ticket = a.ws_tickets + ((size_t)tok * gridDim.y + block) * a.CS + rank;
     if (tid == 0) {
       const int t = atomicAdd(ticket, 1);
       *last_flag = (t == a.KG - 1);
@@ -730,14 +733,14 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       for (int i = 0; i < l2_threads<CW, COPY>() / 32; ++i) tot += rowsum[i];
       // slot = (row block, rank): with K groups only the CTA that finished the rows writes, so
       // every slot is written exactly once per launch, whichever K group came last
-      a.ssq[(size_t)tok * (gridDim.x / a.KG) + block * a.CS + rank] = tot;
+      a.ssq[((size_t)tok * gridDim.y + block) * a.CS + rank] = tot;
     }
   }
   // ---- fused all-reduce: the last CTA of the launch advances this rank's epoch ----
   if (efl & 1) {
     __syncthreads();
     if (tid == 0) {
-      const unsigned int n_cta = gridDim.x * gridDim.y;
+      const unsigned int n_cta = gridDim.x * gridDim.y * gridDim.z;
       if (atomicAdd(a.ar_state + 1, 1u) == n_cta - 1) {
         a.ar_state[1] = 0u;
         __threadfence();
@@ -874,7 +877,7 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
         const int smem = smem_of(stages);
         if (smem > smem_cap) continue;
         const int64_t clusters = lut2_blocks(part_sizes, n_parts, n, rows) * kg * t;
-        if (clusters * cs > 65535 * 8) continue;
+        if (lut2_blocks(part_sizes, n_parts, n, rows) > 65535 || t > 65535) continue;   // grid.y, grid.z
         const int64_t waves = (clusters + slots1 - 1) / slots1;
         // narrower clusters stream narrower strips of the code matrix and measured ~20 % slower per
         // row iteration; K groups only where they clearly pay (profiles/r1_18_microbench_lut_tma.jsonl)
@@ -998,7 +1001,7 @@ static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl
     attr_set[dev & 63] = true;
   }
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(a.parts.cta_end[a.parts.n_parts - 1] * pl.kg * pl.cs, a.T, 1);
+  cfg.gridDim = dim3(pl.kg * pl.cs, a.parts.cta_end[a.parts.n_parts - 1], a.T);
   cfg.blockDim = dim3(l2_threads<CW, COPY>());
   cfg.dynamicSmemBytes = pl.smem_total;
   cfg.stream = stream;
@@ -1009,7 +1012,7 @@ static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 2 : 1;
   if (a.trace) {                                   // diagnostics only (tools/trace_lut.py)
-    g_lut_last_grid[0] = cfg.gridDim.x; g_lut_last_grid[1] = cfg.gridDim.y;
+    g_lut_last_grid[0] = cfg.gridDim.x * cfg.gridDim.y; g_lut_last_grid[1] = cfg.gridDim.z;
     g_lut_last_grid[2] = pl.cs; g_lut_last_grid[3] = pl.smem_total;
   }
   return (int)cudaLaunchKernelEx(&cfg, kern, map, a);
@@ -1063,10 +1066,11 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.x = x; a.codebooks = codebooks; a.scales = scales; a.bias = bias;
   a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
+  a.m_log2 = m == 1 ? 0 : m == 2 ? 1 : 2;
   a.Gp = (int)(k / d * m); a.R = 1; a.n_tiles = pl.n_tiles;
   a.codes = (const unsigned char*)codes;
   a.copy_w = a.Gp % 16 == 0 ? 0 : (a.Gp % 8 == 0 ? 8 : 4);
-  a.S = pl.S; a.CS = pl.cs;
+  a.S = pl.S; a.CS = pl.cs; a.cs_log2 = lut2_log2(pl.cs);
   a.rows_per_cluster = pl.rows_per_cluster; a.stages = pl.stages; a.KG = pl.kg;
   if (pl.kg > 1) {
     const int64_t blocks = lut2_blocks(part_sizes, n_parts, n, pl.rows_per_cluster);
