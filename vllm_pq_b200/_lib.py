@@ -11,7 +11,8 @@ import os
 from ctypes import c_char_p, c_int, c_int64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpq_b200.so")
+# PQ_B200_LIB: another build of the same library (timing experiments); the default is the in-tree one
+LIB_PATH = os.environ.get("PQ_B200_LIB") or os.path.join(_HERE, "libpq_b200.so")
 
 PQ_F16, PQ_BF16 = 0, 1
 ALGO_AUTO, ALGO_GEMV_DIRECT, ALGO_GEMV_LUT, ALGO_GEMM_TC, ALGO_GEMM_MMA, ALGO_GEMV_LUT_TMA = 0, 1, 2, 3, 4, 5

@@ -148,7 +148,11 @@ __device__ __forceinline__ float l2_allreduce_row(const Lut2Args& a, int tok, in
 }
 
 constexpr int kL2TraceSlots = 16;
+// Phase stamps (tools/trace_lut.py) are compiled into the TRACE instantiations only (fp16, d = 8, no
+// mask): a dozen predicated stamp sequences on the latency-critical path are not free for 17 warps.
+template <bool TRACE>
 __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
+  if constexpr (!TRACE) return;
   if (a.trace != nullptr && threadIdx.x == 0 && ((a.trace_mask >> slot) & 1)) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -158,7 +162,9 @@ __device__ __forceinline__ void l2_trace(const Lut2Args& a, int slot) {
 
 // BAR.SYNC does not block at issue: a stamp right after a barrier shows when this warp ARRIVED.
 // This one waits for `dep` (a value read after the barrier from another warp's data) first.
+template <bool TRACE>
 __device__ __forceinline__ void l2_trace_dep(const Lut2Args& a, int slot, const volatile uint32_t* p) {
+  if constexpr (!TRACE) return;
   if (a.trace != nullptr && threadIdx.x == 0 && ((a.trace_mask >> slot) & 1)) {
     const uint32_t dep = *p;
     unsigned long long t;
@@ -356,7 +362,7 @@ template <int CW, int COPY> constexpr int l2_threads() { return CW * 32 + 32 * (
 // residual add, sums of squares).  A template parameter, not run-time flags: with run-time flags
 // alone the plain launch measured 0.3 us slower (profiles/r2_12_ab.txt) - set-up code of the fused
 // steps hoisted onto the latency-critical path after the dependency wait and before the stores.
-template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED>
+template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED, bool TRACE = false>
 __global__ void __launch_bounds__(l2_threads<CW, COPY>(), CW <= 8 ? 2 : 1)
 pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) {
   constexpr int kL2ConsWarps = CW;
@@ -380,13 +386,18 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   const int rank = clustered ? (int)l2_cluster_rank() : 0;
   // grid = (CS * KG, row blocks, tokens): no division to find this CTA's place
   const int tok = blockIdx.z;
-  l2_trace(a, 0);
+  l2_trace<TRACE>(a, 0);
   // every CTA of the cluster has started once this barrier phase completes (waited for just before
   // the first distributed-shared-memory store, long after everyone arrived)
   if (clustered) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
   const int block = blockIdx.y, kg = blockIdx.x >> a.cs_log2;   // cluster: (row block, K group)
   const int tile0 = kg * a.CS * a.S + rank;        // this CTA's tiles: tile0, tile0 + CS, ... (S of them)
-  const RowBlock rb = locate_row_block(a.parts, block, a.rows_per_cluster);
+  RowBlock rb;
+  if (a.parts.n_parts == 1) {                      // o_proj, down_proj: no partition walk
+    rb.part = 0; rb.row0 = block * a.rows_per_cluster; rb.row1 = min(rb.row0 + a.rows_per_cluster, a.N);
+  } else {
+    rb = locate_row_block(a.parts, block, a.rows_per_cluster);
+  }
   const int rows = rb.row1 - rb.row0;
   const int n_iter = (rows + kL2Cons - 1) / kL2Cons;
   // tiles of this CTA that exist (the last K group may leave some ranks with none)
@@ -417,7 +428,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  l2_trace(a, 8);
+  l2_trace<TRACE>(a, 8);
 
   if (warp >= kL2ConsWarps) {
     // ================= producer warp: the whole code stream of this CTA, weights only ===========
@@ -570,10 +581,10 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       }
     };
 
-    l2_trace(a, 1);
+    l2_trace<TRACE>(a, 1);
     pdl_launch_dependents();                       // the next layer may start fetching its weights
     pdl_wait();                                    // x comes from the previous kernel
-    l2_trace(a, 2);
+    l2_trace<TRACE>(a, 2);
     // fused all-reduce: this launch's epoch.  The counter is advanced by the last CTA of the previous
     // fused launch, which has completed by now; parked in shared memory, not in a register that
     // would live across the lookup loop.
@@ -607,27 +618,27 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         }
       }
     }
-    l2_trace(a, 11);
+    l2_trace<TRACE>(a, 11);
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-    l2_trace(a, 12);
+    l2_trace<TRACE>(a, 12);
     l2_cons_sync<kL2Cons>();
-    l2_trace_dep(a, 3, reinterpret_cast<const volatile uint32_t*>(xs) + 255);
+    l2_trace_dep<TRACE>(a, 3, reinterpret_cast<const volatile uint32_t*>(xs) + 255);
 
     for (int s = 0; s < my_tiles; ++s) {
       if (s > 0) l2_cons_sync<kL2Cons>();                   // everyone is done with the previous table
       l2_build_table<T, D, CW>(lut, cbs, xs + (size_t)s * l2_x_words<D>() * 2, a.E, a.M, warp, lane);
-      if (s == 0) l2_trace(a, 10);
+      if (s == 0) l2_trace<TRACE>(a, 10);
       l2_cons_sync<kL2Cons>();
-      if (s == 0) l2_trace_dep(a, 4, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
-      if (s == 1) l2_trace_dep(a, 13, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
+      if (s == 0) l2_trace_dep<TRACE>(a, 4, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
+      if (s == 1) l2_trace_dep<TRACE>(a, 13, reinterpret_cast<const volatile uint32_t*>(lut) + (a.E - 1) * kL2Tile + 63);
       if (s + 1 == my_tiles && clustered) asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
       for (int it = 0; it < n_iter; ++it) {
         uint32_t cw[4][4];
         load_codes(cw, it);
         lookups(cw, s, it);
-        if (s == 0 && it == 0) l2_trace(a, 9);
-        if (s == 1 && it == 0) l2_trace(a, 14);
-        if (s == 0 && it == n_iter - 1) l2_trace(a, 15);
+        if (s == 0 && it == 0) l2_trace<TRACE>(a, 9);
+        if (s == 1 && it == 0) l2_trace<TRACE>(a, 14);
+        if (s == 0 && it == n_iter - 1) l2_trace<TRACE>(a, 15);
       }
     }
     if (my_tiles == 0) {                           // no tile in this K group: contribute zeros
@@ -644,7 +655,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
         for (int i = tid; i < rows; i += kL2Cons) rowsum[i] = 0.f;
       }
     }
-    l2_trace(a, 5);
+    l2_trace<TRACE>(a, 5);
   }
 
   // ---- split-K over the cluster: the partial sums of rows [o, o+1) * chunk were pushed into CTA
@@ -658,7 +669,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
   } else {
     __syncthreads();
   }
-  l2_trace(a, 6);
+  l2_trace<TRACE>(a, 6);
   // One finished row: (all-reduce over the TP ranks,) one rounding of y, (residual add,) store.
   // (the plain launch pays one flag test here: the fused steps sit behind it, their loops not unrolled,
   // so that nothing of theirs is hoisted onto the plain path - measured 0.3 us per launch when it was)
@@ -748,7 +759,7 @@ pq_gemv_lut2_kernel(const __grid_constant__ CUtensorMap tmap, const Lut2Args a) 
       }
     }
   }
-  l2_trace(a, 7);
+  l2_trace<TRACE>(a, 7);
 }
 
 // ------------------------------------------------------------------ host side
@@ -987,9 +998,9 @@ static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED>
+template <typename T, int D, bool MASK, bool COPY, int CW, bool FUSED, bool TRACE = false>
 static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
-  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY, CW, FUSED>;
+  auto kern = pq_gemv_lut2_kernel<T, D, MASK, COPY, CW, FUSED, TRACE>;
   static bool attr_set[64] = {};                   // per instantiation, per device
   int dev = 0;
   cudaGetDevice(&dev);
@@ -1020,6 +1031,11 @@ static int launch_lut2_c(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl
 
 template <typename T, int D, bool MASK>
 static int launch_lut2(const CUtensorMap& map, Lut2Args& a, const Lut2Plan& pl, cudaStream_t stream) {
+  if constexpr (std::is_same<T, __half>::value && D == 8 && !MASK) {      // phase trace: the bench's instantiation only
+    if (a.trace != nullptr && !a.copy_w && !a.ep_flags && a.xact != 2)
+      return pl.cw == 8 ? launch_lut2_c<T, D, false, false, 8, false, true>(map, a, pl, stream)
+                        : launch_lut2_c<T, D, false, false, 16, false, true>(map, a, pl, stream);
+  }
   if constexpr (!MASK) {                           // fused steps: 8-bit codes only (gemv_lut2_fused_supported)
     if (a.ep_flags || a.xact == 2) {
       if (pl.cw == 8)
