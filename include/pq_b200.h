@@ -165,6 +165,12 @@ typedef struct {
   int32_t norm_slots;
   float norm_eps;
   int32_t input_silu_mul;        /* 1: x is [t, 2k] = (gate | up), the input is SiLU(gate) * up   */
+  /* Private repacked copy of `codes` built once by process_weights_after_loading (base_config.py:37-42,
+   * model_loader/loader.py:157-168): the same bytes with every row padded to codes_pitch bytes, a
+   * multiple of 16, so that rows whose code bytes are not (the TP = 4 / 8 shards of Llama-2-7B's
+   * down_proj: 344 / 172 bytes) can be streamed by TMA.  NULL: `codes` itself is streamed. */
+  const void* codes_padded;
+  int64_t codes_pitch;
 } pq_b200_epilogue_t;
 
 /* pq_b200_gemm on the table GEMV (PQ_ALGO_GEMV_LUT_TMA) with the extras above; PQ_ERR_UNSUPPORTED when

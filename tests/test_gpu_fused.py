@@ -139,3 +139,38 @@ def test_layer_api_fused_chain_matches_separate_launches():
             assert torch.equal(z, z_ref)
         rel = float((y.double() - y_ref.double()).pow(2).mean().sqrt() / y_ref.double().pow(2).mean().sqrt())
         assert rel < 1e-3, (t, rel)
+
+
+@pytest.mark.parametrize("k", [1376, 2752, 8 * 100])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2), (4, 8, 1)])
+def test_padded_codes_copy(k, fmt):
+    """process_weights_after_loading pads code rows that are not a multiple of 16 bytes (TP = 4 / 8
+    shards of down_proj) into a private copy for the TMA stream: same bits as the cp.async loader
+    over the checkpoint layout, dequant untouched."""
+    b, d, m = fmt
+    dtype = torch.float16
+    cfg = P.PQConfig(d, b, m, 1)
+    c = O.make_case([4096], k, b, d, m, t=8, dtype=dtype, seed=41)
+    c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).to(dtype)
+    with torch.device("cuda"):
+        lin = P.RowParallelLinear(k, 4096, bias=False, params_dtype=dtype, quant_config=cfg)
+    lin.codes.data.copy_(c["codes"]); lin.codebooks.data.copy_(c["codebooks"]); lin.scales.data.copy_(c["scales"])
+    row = (k // d) * m
+    assert not hasattr(lin, "codes_padded")
+    x = c["x"].cuda()
+    before = {t: lin(x[:t])[0] for t in (1, 3, 8)}
+    lin.quant_method.process_weights_after_loading(lin)
+    if row % 16:
+        assert lin.codes_padded.shape == (4096, (row + 15) // 16 * 16)
+    else:
+        assert not hasattr(lin, "codes_padded")
+    for t in (1, 3, 8):
+        y, _ = lin(x[:t])
+        ct = dict(c); ct["x"] = c["x"][:t]
+        ref = O.linear_fp32(ct["x"], c["codes"], c["codebooks"], c["scales"], [4096], None)
+        assert O.error_report(y.cpu(), ref)["rms_rel"] < RMS_REL_TOL[dtype]
+        if t == 1 and b == 8:         # same kernel, same order of sums: the loader does not change a bit
+            assert torch.equal(y, before[t])
+    w = lin.quant_method.dequantize(lin, scaled=True)
+    w_ref = O.dequantize_partitions(c["codes"], c["codebooks"], [4096], c["scales"])
+    assert torch.equal(w.cpu().view(torch.int16), w_ref.view(torch.int16))

@@ -35,7 +35,8 @@ _LIBRARY.define("gemm_silu_mul(Tensor input, Tensor codes, Tensor codebooks, Ten
 _LIBRARY.define("silu_and_mul(Tensor input) -> Tensor")
 _LIBRARY.define("gemm_fused(Tensor input, Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes, Tensor? bias, Tensor? residual, Tensor? norm_ssq, "
-                "Tensor? norm_weight, float norm_eps, bool allreduce, bool silu_mul, bool want_ssq) -> (Tensor, Tensor)")
+                "Tensor? norm_weight, float norm_eps, bool allreduce, bool silu_mul, bool want_ssq, "
+                "Tensor? codes_padded) -> (Tensor, Tensor)")
 _LIBRARY.define("fused_add_rms_norm(Tensor(a!) input, Tensor(b!)? residual, Tensor weight, float epsilon) -> ()")
 _LIBRARY.define("dequant(Tensor codes, Tensor codebooks, int[] codebook_partition_sizes) -> Tensor")
 _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
@@ -173,7 +174,7 @@ def gemm_fused_supported(t: int, n: int, k: int, d: int, nbits: int, m: int) -> 
 
 
 def _gemm_fused_cuda(input, codes, codebooks, scales, parts, bias, residual, norm_ssq, norm_weight, norm_eps,
-                     allreduce, silu_mul, want_ssq):
+                     allreduce, silu_mul, want_ssq, codes_padded=None):
     """pq_b200_gemm_fused: the table GEMV with (norm on the x load | SiLU*mul on the x load), and in its
     epilogue (all-reduce over the TP group,) (residual add,) (sum of squares per CTA).  SURVEY 8f N1."""
     _require_cuda(input)
@@ -215,6 +216,11 @@ def _gemm_fused_cuda(input, codes, codebooks, scales, parts, bias, residual, nor
         ep.norm_slots, ep.norm_eps = nss.shape[1], float(norm_eps)
         keep.append(nss)
     ep.input_silu_mul = 1 if silu_mul else 0
+    if codes_padded is not None:
+        if (codes_padded.dim() != 2 or codes_padded.shape[0] != n or codes_padded.shape[1] < g * m
+                or codes_padded.element_size() != 1 or not codes_padded.is_contiguous()):
+            raise RuntimeError("PQ: codes_padded must be a contiguous [N, pitch] byte tensor, pitch >= G * M")
+        ep.codes_padded, ep.codes_pitch = codes_padded.data_ptr(), codes_padded.shape[1]
     arr, np_ = _lib.parts_array(parts)
     out = torch.empty((t, n), dtype=dt, device=input.device)
     with torch.cuda.device(input.device):
@@ -335,7 +341,7 @@ torch.library.register_fake("pq::gemm_silu_mul")(_gemm_algo_fake)
 torch.library.register_fake("pq::silu_and_mul")(
     lambda input: torch.empty(input.shape[:-1] + (input.shape[-1] // 2,), dtype=input.dtype, device=input.device))
 def _gemm_fused_fake(input, codes, codebooks, scales, codebook_partition_sizes, bias, residual, norm_ssq,
-                     norm_weight, norm_eps, allreduce, silu_mul, want_ssq):
+                     norm_weight, norm_eps, allreduce, silu_mul, want_ssq, codes_padded=None):
     n = codes.size(0)
     y = torch.empty(input.shape[:-1] + (n,), dtype=input.dtype, device=input.device)
     t = y.numel() // n
@@ -375,12 +381,12 @@ def pq_gemm_fused(input: torch.Tensor, codes: torch.Tensor, codebooks: torch.Ten
                   codebook_partition_sizes: List[int], bias: Optional[torch.Tensor] = None, *,
                   residual: Optional[torch.Tensor] = None, norm_ssq: Optional[torch.Tensor] = None,
                   norm_weight: Optional[torch.Tensor] = None, norm_eps: float = 1e-6, allreduce: bool = False,
-                  silu_mul: bool = False, want_ssq: bool = False):
+                  silu_mul: bool = False, want_ssq: bool = False, codes_padded: Optional[torch.Tensor] = None):
     """(y, ssq): the decode table GEMV with its fused prologue / epilogue (include/pq_b200.h,
     pq_b200_gemm_fused).  Replaces apply -> all_reduce -> fused_add_rms_norm -> ... of
     linear.py:1209-1213 / llama.py:272-286 at decode."""
     return torch.ops.pq.gemm_fused(input, codes, codebooks, scales, codebook_partition_sizes, bias, residual,
-                                   norm_ssq, norm_weight, norm_eps, allreduce, silu_mul, want_ssq)
+                                   norm_ssq, norm_weight, norm_eps, allreduce, silu_mul, want_ssq, codes_padded)
 
 
 def fused_add_rms_norm(input: torch.Tensor, residual: Optional[torch.Tensor], weight: torch.Tensor,

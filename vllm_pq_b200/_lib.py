@@ -33,7 +33,8 @@ class Epilogue(ctypes.Structure):
                 ("ar_state", c_void_p), ("ar_slot_elems", c_int64), ("residual", c_void_p),
                 ("residual_stride", c_int64), ("ssq_out", c_void_p), ("ssq_slots", c_int64),
                 ("norm_ssq", c_void_p), ("norm_weight", c_void_p), ("norm_slots", ctypes.c_int32),
-                ("norm_eps", ctypes.c_float), ("input_silu_mul", ctypes.c_int32)]
+                ("norm_eps", ctypes.c_float), ("input_silu_mul", ctypes.c_int32),
+                ("codes_padded", c_void_p), ("codes_pitch", c_int64)]
 
 
 SIGNATURES = {

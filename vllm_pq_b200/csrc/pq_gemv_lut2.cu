@@ -985,11 +985,11 @@ static PFN_l2TmapEncodeTiled lut2_tmap_encoder() {
 
 // codes [N, Gp] bytes, row-major, as a 2-D tensor map: box = 64 code bytes x 64 rows, no swizzle,
 // out-of-bounds rows and positions read as zero.
-static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64_t gp, int R) {
+static int lut2_codes_tmap(CUtensorMap* map, const void* codes, int64_t n, int64_t gp, int64_t pitch) {
   PFN_l2TmapEncodeTiled enc = lut2_tmap_encoder();
   if (!enc) return PQ_ERR_UNSUPPORTED;
-  const cuuint64_t gdim[2] = {(cuuint64_t)(gp * R), (cuuint64_t)(n / R)};
-  const cuuint64_t gstride[1] = {(cuuint64_t)(gp * R)};
+  const cuuint64_t gdim[2] = {(cuuint64_t)gp, (cuuint64_t)n};
+  const cuuint64_t gstride[1] = {(cuuint64_t)pitch};
   const cuuint32_t box[2] = {(cuuint32_t)kL2Tile, (cuuint32_t)kL2BoxRows};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(codes), gdim, gstride, box, estr,
@@ -1134,7 +1134,13 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   int rc = make_parts(a.parts, part_sizes, n_parts, n, pl.rows_per_cluster);
   if (rc) return rc;
   CUtensorMap map;
-  rc = lut2_codes_tmap(&map, codes, n, a.copy_w ? (a.Gp + 15) / 16 * 16 : a.Gp, 1);   // unused when copy_w
+  const bool padded = ep != nullptr && ep->codes_padded != nullptr;
+  if (padded) {
+    if (ep->codes_pitch % 16 || ep->codes_pitch < a.Gp || ((uintptr_t)ep->codes_padded & 15)) return PQ_ERR_ALIGN;
+    a.copy_w = 0;
+  }
+  const int64_t pitch = padded ? ep->codes_pitch : (a.Gp + 15) / 16 * 16;          // map unused when copy_w
+  rc = lut2_codes_tmap(&map, padded ? ep->codes_padded : codes, n, padded ? a.Gp : pitch, pitch);
   if (rc) return rc;
   return dtype == PQ_F16 ? launch_lut2_d<__half>(map, a, d, pl, stream)
                          : launch_lut2_d<__nv_bfloat16>(map, a, d, pl, stream);

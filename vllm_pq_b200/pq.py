@@ -151,17 +151,44 @@ class PQLinearMethodBody:
             set_weight_attrs(p, extra_weight_attrs)
 
     def process_weights_after_loading(self, layer: torch.nn.Module) -> None:
-        # The kernels read the checkpoint layout directly; nothing to repack. Make the
-        # contiguity the op requires explicit once, instead of per call.
+        """The hook vLLM calls once after the checkpoint tensors are in place (base_config.py:37-42,
+        model_loader/loader.py:157-168).  The kernels read the checkpoint layout directly, so the
+        parameters stay as loaded (contiguity made explicit once, not per call).  One private repack
+        (SURVEY.md 8f N3): 8-bit-or-narrower codes whose row is not a multiple of 16 bytes - the
+        row-parallel shards of down_proj at TP = 4 / 8 (344 / 172 bytes) - get a copy with the row
+        pitch padded to 16 bytes, ``layer.codes_padded`` [N, pitch]: TMA cannot address the unpadded
+        rows, and the cp.async loader that serves them reads 1.27 x the bytes.  The decode table GEMV
+        streams the copy; every other kernel (and pq::dequant) keeps reading ``codes``."""
         for name in ("codes", "codebooks", "scales"):
             p = getattr(layer, name)
             if not p.data.is_contiguous():
                 p.data = p.data.contiguous()
+        codes = layer.codes.data
+        n, g, m = codes.shape
+        row = g * m * codes.element_size()
+        if codes.element_size() == 1 and row % 16 and row >= 64 and codes.is_cuda:
+            pitch = (row + 15) // 16 * 16
+            padded = torch.zeros((n, pitch), dtype=codes.dtype, device=codes.device)
+            padded[:, :row] = codes.view(n, row)
+            layer.codes_padded = padded
+        elif hasattr(layer, "codes_padded"):
+            del layer.codes_padded
+
+    def _decode_fused_ok(self, layer: torch.nn.Module, x: torch.Tensor) -> bool:
+        n, g, m = layer.codes.shape
+        d, nbits = layer.codebooks.shape[3], layer.codebooks.shape[1].bit_length() - 1
+        t = x.numel() // x.shape[-1] if x.shape[-1] else 0
+        return x.is_cuda and t >= 1 and ops.gemm_fused_supported(t, n, g * d, d, nbits, m)
 
     def apply(self, layer: torch.nn.Module, x: torch.Tensor,
               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         codebooks = layer.codebooks
         output_partition_sizes = getattr(codebooks, "output_partition_sizes", [])
+        padded = getattr(layer, "codes_padded", None)
+        if padded is not None and self._decode_fused_ok(layer, x):
+            # decode over the padded private copy (process_weights_after_loading)
+            return ops.pq_gemm_fused(x, layer.codes, codebooks, layer.scales, list(output_partition_sizes),
+                                     bias, codes_padded=padded)[0]
         # One op for every token count and format: the C side picks GEMV (decode) or the
         # tcgen05 GEMM (prefill). Reference dispatch for comparison: aqlm.py:344-374.
         return ops.pq_gemm(x, layer.codes, codebooks, layer.scales,
@@ -171,8 +198,12 @@ class PQLinearMethodBody:
                        bias: Optional[torch.Tensor] = None) -> torch.Tensor:
         """apply(SiLU(x[..., :k]) * x[..., k:]): act_fn + down_proj of the MLP (llama.py:89-93)."""
         codebooks = layer.codebooks
-        return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales,
-                                    list(getattr(codebooks, "output_partition_sizes", [])), bias)
+        parts = list(getattr(codebooks, "output_partition_sizes", []))
+        padded = getattr(layer, "codes_padded", None)
+        if padded is not None and self._decode_fused_ok(layer, x[..., : x.shape[-1] // 2]):
+            return ops.pq_gemm_fused(x, layer.codes, codebooks, layer.scales, parts, bias, silu_mul=True,
+                                     codes_padded=padded)[0]
+        return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales, parts, bias)
 
     def apply_fused(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
                     residual: Optional[torch.Tensor] = None, norm=None, allreduce: bool = False,
@@ -200,7 +231,8 @@ class PQLinearMethodBody:
             ns, nw, ne = norm if norm is not None else (None, None, 1e-6)
             y, ssq = ops.pq_gemm_fused(x, codes, codebooks, layer.scales, parts, bias, residual=residual,
                                        norm_ssq=ns, norm_weight=nw, norm_eps=ne, allreduce=allreduce,
-                                       silu_mul=silu_mul, want_ssq=want_ssq)
+                                       silu_mul=silu_mul, want_ssq=want_ssq,
+                                       codes_padded=getattr(layer, "codes_padded", None))
             return y, (ssq if want_ssq else None)
         y = (ops.pq_gemm_silu_mul if silu_mul else ops.pq_gemm)(x, codes, codebooks, layer.scales, parts, bias)
         if allreduce:
