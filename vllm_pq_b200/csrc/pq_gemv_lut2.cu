@@ -857,7 +857,7 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
     const int cons = cw * 32;
     const int smem_cap = cw == 8 ? kL2TwoPerSm : 220 * 1024;
     for (int cs = 1; cs <= kL2MaxCluster; cs *= 2) {
-      if (cs > pl.n_tiles) break;
+      if (cs > 1 && cs / 2 >= pl.n_tiles) break;   // up to the next power of two: the ranks left without a tile add zeros
       if (force_cs && cs != force_cs) continue;
       if (cs == 16 && !force_cs && cw == 16) continue;           // 16-CTA clusters: the small shape only
       int slots1 = lut2_cluster_slots(cw, cs, cw == 8 ? 100 * 1024 : 200 * 1024);
