@@ -46,6 +46,14 @@ def measured_peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def measured_tc_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as fh:
+            return float(json.load(fh)["bf16_tflops"])
+    return 1650.0
+
+
 def measured_traffic(model: str, fmt: str, dtype: str, world: int, batch: int, kernel: str):
     """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None."""
     path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
@@ -139,31 +147,50 @@ def cpu_layer_time(fmt, batch, dtype, repeats, n_layers_total=32):
 
 
 def run_reference_arm(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.  One step =
+    one bounded sample of the workload: the four PQ linears of ONE decoder layer (1/32 of the
+    Llama-2-7B step) through the oracle's literal port of generic_dequantize_gemm (aqlm.py:94-127:
+    unpack, embedding_bag, scale, F.linear - /root/reference is absent on the GPU box).  Exactly
+    --warmup untimed and --steps timed samples run; ms_per_step is what was timed, `value`
+    extrapolates it to the whole 32-layer step (every layer does identical work)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import pq_oracle as O
     fmt = parse_format(args.format)
+    b, d, m = fmt
     dtype = torch.float16 if args.dtype == "fp16" else torch.bfloat16
     layers = 32
-    # W warm-up + K timed steps, each step = one decoder layer's linears (1/32 of the workload)
-    best, med = cpu_layer_time(fmt, args.batch, dtype, repeats=max(1, min(args.steps, 5)))
-    step_s = med * layers
-    value = args.batch / step_s
+    torch.set_num_threads(os.cpu_count() or 1)
+    shapes = [([4096] * 3, 4096), ([4096], 4096), ([11008] * 2, 4096), ([4096], 11008)]
+    cases = [O.make_case(parts, k, b, d, m, t=args.batch, dtype=dtype, seed=i) for i, (parts, k) in enumerate(shapes)]
+
+    def sample():
+        for c in cases:
+            O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"],
+                                      c["partition_sizes"], None, literal=True)
+    for _ in range(max(1, args.warmup)):
+        sample()
+    steps = max(1, min(args.steps, 200))
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        sample()
+    sample_s = (time.perf_counter() - t0) / steps
+    value = args.batch / (sample_s * layers)
     cores = torch.get_num_threads()
-    sample = (f"1 of {layers} decoder layers (qkv,o,gate_up,down) per step, x{layers} extrapolated; "
-              f"oracle port of aqlm.py:94-127 (unpack, embedding_bag, scale, F.linear), {args.dtype}")
+    desc = (f"one step = 1 of {layers} decoder layers (qkv,o,gate_up,down), {steps} timed; value extrapolates x{layers}; "
+            f"oracle port of aqlm.py:94-127 (unpack, embedding_bag, scale, F.linear), {args.dtype}")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
+        "steps": steps, "warmup": max(1, args.warmup), "ms_per_step": sample_s * 1e3, "extrapolated_x": layers,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f16" if dtype == torch.float16 else "bf16", "data": "synthetic",
-        # the same workload description as the GPU arm prints (run_gpu_arm); the CPU arm has no
-        # launch / all-reduce modes, and its L2 note does not apply
+        # the same keys and workload description as the GPU arm prints (run_gpu_arm)
         "config": {"workload": f"{args.model} all PQ linears ({layers} layers x qkv,o,gate_up,down), decode",
                    "batch": args.batch, "format": f"{fmt[0]}bit x d{fmt[1]} x M{fmt[2]}",
                    "parallelism": f"tp{args.gpus}", "cold_l2": "n/a (host cores)", "launch": "n/a (host cores)",
-                   "allreduce": "none"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                   "allreduce": "none", "mlp_act": "n/a (linears only)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -239,6 +266,118 @@ def check_result(model, x_dev, y_dev, world, n_layers=2):
     res["ok"] = res["finite"] and res["max_rms_rel"] < tol
     res["tol_rms_rel"] = tol
     return res
+
+
+# ------------------------------------------------------------------------------------------
+# the rest of BASELINE.json's metric, outside the headline's timed region (rank 0, one GPU)
+# ------------------------------------------------------------------------------------------
+def _time_sets(fn, sets, iters, stream):
+    """One CUDA graph holding one call per (distinct) weight set - codes never stay L2-resident -
+    replayed `iters` times between events on the launching stream; seconds per call."""
+    with torch.cuda.stream(stream):
+        for s_ in sets[:2]:
+            fn(s_)
+        stream.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            keep = [fn(s_) for s_ in sets]
+        for _ in range(3):
+            g.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        stream.synchronize()
+        e0.record(stream)
+        for _ in range(iters):
+            g.replay()
+        e1.record(stream)
+        stream.synchronize()
+    del keep
+    return e0.elapsed_time(e1) * 1e-3 / (iters * len(sets))
+
+
+def _make_sets(parts, k, b, d, m, dtype, device, min_bytes=256 << 20, max_sets=64):
+    n, e = sum(parts), 1 << b
+    code_bytes = n * (k // d) * m * (1 if b <= 8 else 2)
+    nrep = max(2, min(max_sets, min_bytes // code_bytes + 1))
+    sets = []
+    for _ in range(nrep):
+        codes = torch.randint(-(e // 2), e // 2, (n, k // d, m), device=device, dtype=torch.int32).to(
+            torch.int8 if b <= 8 else torch.int16)
+        cb = torch.randn(len(parts) * m, e, 1, d, device=device, dtype=dtype) / (k * m) ** 0.5
+        sc = (torch.rand(n, 1, 1, 1, device=device) + 0.5).to(dtype)
+        sets.append((codes, cb, sc))
+    return sets, code_bytes
+
+
+def _algo_bytes(t, n, k, d, b, m, p):
+    return n * (k // d) * m * (1 if b <= 8 else 2) + p * m * (1 << b) * d * 2 + n * 2 + t * k * 2 + t * n * 2
+
+
+def run_extras(P, S, device, stream, hbm_gbs, tc_peak, clk_index):
+    """configs 1, 3, 5, the 70B layer shapes and the same-box reference kernels."""
+    out = {}
+    dt = torch.float16
+
+    def gemv(parts, k, b, d, m, t=1, iters=20):
+        sets, _ = _make_sets(parts, k, b, d, m, dt, device)
+        x = torch.randn(t, k, device=device, dtype=dt)
+        sec = _time_sets(lambda s_: P.ops.pq_gemm(x, s_[0], s_[1], s_[2], parts, None), sets, iters, stream)
+        ab = _algo_bytes(t, sum(parts), k, d, b, m, len(parts))
+        row = {"us": sec * 1e6, "gbs": ab / sec / 1e9, "frac": ab / sec / 1e9 / hbm_gbs}
+        return row, sets, x
+
+    # config 1: single 4096 x 4096 linear, 8 bit x d8 x M1, one token
+    out["gemv_single"], _, _ = gemv([4096], 4096, 8, 8, 1)
+    out["gemv_single"]["workload"] = "config 1: 4096x4096, 8bit x d8 x M1, batch 1"
+    # config 5: 4/8/12-bit codes x subvector 4/8/16, 4096 x 4096, one token
+    out["sweep"] = {}
+    for b in (4, 8, 12):
+        for d in (4, 8, 16):
+            out["sweep"][f"{b}x{d}x1"] = gemv([4096], 4096, b, d, 1, iters=10)[0]
+    # Llama-2-70B layer shapes, one token, 8 bit x d8 x M1
+    out["llama70b_layer"] = {}
+    for name, parts, k in (("qkv_proj", [8192, 1024, 1024], 8192), ("o_proj", [8192], 8192),
+                           ("gate_up_proj", [28672] * 2, 8192), ("down_proj", [8192], 28672)):
+        out["llama70b_layer"][name] = gemv(parts, k, 8, 8, 1, iters=10)[0]
+    # config 3: Llama-3-8B MLP shapes, 2048 tokens (tcgen05 GEMM), with the same-box baselines
+    have_ref = False
+    try:
+        from oracle import ref_cuda as R                    # checker / baseline only
+        have_ref = R.available()
+    except Exception:
+        R = None
+    out["prefill"] = {}
+    with ClockSampler(clk_index) as clk:
+        for name, parts, k in (("gate_up8b", [14336] * 2, 4096), ("down8b", [4096], 14336)):
+            n, t = sum(parts), 2048
+            for (b, d, m) in ((8, 8, 1), (8, 8, 2), (16, 8, 1)):
+                sets, _ = _make_sets(parts, k, b, d, m, dt, device, max_sets=8)
+                x = torch.randn(t, k, device=device, dtype=dt)
+                sec = _time_sets(lambda s_: P.ops.pq_gemm(x, s_[0], s_[1], s_[2], parts, None), sets, 5, stream)
+                row = {"us": sec * 1e6, "tflops": 2 * t * n * k / sec / 1e12, "frac": 2 * t * n * k / sec / 1e12 / tc_peak}
+                if have_ref and R.supports(b, d, m, dt):
+                    rs = _time_sets(lambda s_: R.optimized_dequantize_gemm(x, s_[0], s_[1], s_[2], parts, None),
+                                    sets[:3], 3, stream)
+                    row["ref_cuda_dequant_cublas_us"] = rs * 1e6
+                if (b, d, m) == (8, 8, 1):
+                    dense = [(P.ops.pq_dequant(s_[0], s_[1], parts, s_[2]),) for s_ in sets[:3]]
+                    ds = _time_sets(lambda s_: torch.matmul(x, s_[0].t()), dense, 5, stream)
+                    row["dense_cublas_us"] = ds * 1e6
+                    del dense
+                out["prefill"][f"{name}/{b}x{d}x{m}"] = row
+                del sets
+    out["prefill"]["clocks"] = clk.summary()
+    out["prefill"]["peak_tflops"] = tc_peak
+    # same-box reference kernels at decode (aqlm_gemm: one token, the two formats it supports)
+    if have_ref:
+        out["ref_cuda"] = {}
+        for name, parts, k in (("qkv7b", [4096] * 3, 4096), ("down7b", [4096], 11008), ("gate_up70b", [28672] * 2, 8192)):
+            for (b, d, m) in ((8, 8, 2), (16, 8, 1)):
+                ours, sets, x = gemv(parts, k, b, d, m, iters=10)
+                rs = _time_sets(lambda s_: R.aqlm_gemm(x, s_[0], s_[1], s_[2], parts, None), sets, 5, stream)
+                out["ref_cuda"][f"{name}/{b}x{d}x{m}/t1"] = {"ours_us": ours["us"], "aqlm_gemm_us": rs * 1e6}
+                del sets
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_gpu_arm(args):
@@ -332,6 +471,18 @@ def run_gpu_arm(args):
             kernels[name] = {"us": ms_k * 1e3, "algorithmic_bytes": ab, "gbs": ab / (ms_k * 1e-3) / 1e9}
     clocks = clk.summary()
     checked = check_result(model, x_dev, y_dev, world)      # outside the timed region
+    extras = {}
+    if world == 1 and not args.no_extras:
+        # decode at batch 16 and 64 through the same stack (config 2's other batch sizes)
+        extras["batch"] = {}
+        for bt in (16, 64):
+            xb = torch.randn(bt, shape.hidden, dtype=dtype, device=device)
+            with torch.no_grad():
+                gb, _ = capture(lambda: model(xb), stream)
+            ms_b = timed(lambda: gb.replay(), max(5, args.steps // 5))
+            extras["batch"][str(bt)] = {"tokens_per_s": bt / (ms_b * 1e-3), "ms_per_step": ms_b}
+            del gb
+        extras.update(run_extras(P, S, device, stream, hbm_gbs, measured_tc_peak(), local))
     if world > 1:                                           # every rank must hold the same bits
         ref_y = y_dev.clone()
         dist.broadcast(ref_y, src=0)
@@ -373,6 +524,7 @@ def run_gpu_arm(args):
                          / (ms_step * 1e-3) / 1e9},
             "kernels": kernels,
         }
+        out.update(extras)
         if world == 1 and not args.no_cpu:
             best, med = cpu_layer_time(fmt, B, dtype, repeats=3)
             out["cpu_baseline"] = {
@@ -397,6 +549,8 @@ def main():
     ap.add_argument("--model", default="llama-2-7b")
     ap.add_argument("--pdl", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip configs 1/3/5, batch 16/64, the 70B layer shapes and the same-box reference kernels")
     ap.add_argument("--fused-act", type=int, default=0,
                     help="1: down_proj takes SiLU(gate)*up on its x load (SURVEY 8f N2) instead of the slicing stand-in")
     args = ap.parse_args()
