@@ -38,6 +38,7 @@ SHAPES = {
     "down70b": ([8192], 28672),
     "down7b_tp4": ([4096], 2752),      # row-parallel shards: code pitch 344 / 172 bytes (not a multiple of 16)
     "down7b_tp8": ([4096], 1376),
+    "n4096k1024": ([4096], 1024), "n4096k256": ([4096], 256), "n512k4096": ([512], 4096), "n128k256": ([128], 256),
 }
 
 
@@ -61,17 +62,24 @@ def make(parts, k, b, d, m, dtype, nrep):
 
 def time_loop(fn, sets, iters, graph=True):
     """One CUDA graph holding one call per weight set; replayed `iters` times between events."""
-    for s in sets[:2]:
-        fn(s)
-    torch.cuda.synchronize()
     if graph:
         st = torch.cuda.Stream()
         with torch.cuda.stream(st):
+            # warm up ON the capture stream: the op's workspace is per (device, stream) and is not
+            # allocated during capture - without it the split-K plans are off (as in vLLM, which
+            # also runs a model eagerly on the capture stream first)
+            for s in sets[:2]:
+                fn(s)
+            st.synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=st):
                 keep = [fn(s) for s in sets]
         run = g.replay
     else:
+        for s in sets[:2]:
+            fn(s)
+        torch.cuda.synchronize()
+
         def run():
             for s in sets:
                 fn(s)

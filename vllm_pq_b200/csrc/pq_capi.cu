@@ -119,12 +119,22 @@ static int pick_algo_impl(int64_t t, int64_t n, int64_t k, int d, int nbits, int
   // one token: the TMA-fed table GEMV wins on every Llama projection (profiles/r1_13_microbench_lut2.jsonl)
   if (allow_lut_tma && t == 1 && pq::gemv_lut2_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT_TMA;
   const bool mma_ok = t <= mma_max_t && pq::gemm_mma_supported(t, n, k, d, nbits, m);
+  const bool tc_ok = pq::gemm_tc_supported(t, n, k, d, nbits, m);
+  // Crossovers re-measured in r2 with the split-K tcgen05 kernel (profiles/r2_24, r2_25):
+  //  * 8-bit codes: the mma.sync kernel up to 16 tokens; one codebook keeps it up to 32 tokens on the
+  //    small-N layers (o_proj, down_proj); beyond that the tcgen05 kernel wins everywhere;
+  //  * 16-bit codes (L2-resident 65536-entry books): the gather GEMV for one token and for 2..7
+  //    tokens on layers below 2^27 weights, the tcgen05 kernel otherwise - it gathers each codeword
+  //    once per 128-row tile instead of once per token.
   if (mma_ok) {
-    if (t >= 2 && t <= 16) return PQ_ALGO_GEMM_MMA;
-    if (t == 1 && n < 8192) return PQ_ALGO_GEMM_MMA;
-    if (t > 16 && n < 8192 && m == 1) return PQ_ALGO_GEMM_MMA;
+    if (t <= 16) return PQ_ALGO_GEMM_MMA;
+    if (t <= 32 && m == 1 && n < 8192) return PQ_ALGO_GEMM_MMA;
+    if (!tc_ok) return PQ_ALGO_GEMM_MMA;
   }
-  if (t > 8 && pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ALGO_GEMM_TC;
+  if (tc_ok) {
+    if (nbits > 8 && (t >= 8 || (t >= 2 && n * k >= ((int64_t)1 << 27)))) return PQ_ALGO_GEMM_TC;
+    if (nbits <= 8 && t > 8) return PQ_ALGO_GEMM_TC;
+  }
   if (pq::gemv_lut_preferred(t, n, k, d, nbits, m)) return PQ_ALGO_GEMV_LUT;
   if (mma_ok) return PQ_ALGO_GEMM_MMA;
   return PQ_ALGO_GEMV_DIRECT;
@@ -213,7 +223,7 @@ static int gemm_impl(const void* x, int64_t x_stride, const void* codes, const v
                                    nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
     case PQ_ALGO_GEMM_TC:
       if (!pq::gemm_tc_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
-      if (workspace_bytes < pq::gemm_tc_workspace(t, n, k, d, nbits, m, n_parts)) return PQ_ERR_WORKSPACE;
+      // the workspace is optional (include/pq_b200.h): without it a few-tile problem runs unsplit
       return pq::gemm_tc_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
                                   nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s);
     case PQ_ALGO_GEMV_LUT_TMA:

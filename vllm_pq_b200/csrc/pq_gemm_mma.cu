@@ -340,7 +340,10 @@ static bool mm_plan(MmPlan& pl, int64_t t, int64_t n, int64_t k, int nbits, int 
   const int64_t gp = k / 8 * m;
   const int n_sb = (int)((gp + 63) / 64);
   const int gpv = 16 / m, gps = 64 / m;
-  pl.nb = t <= 8 ? 1 : (t <= 16 ? 2 : 4);
+  // token columns per MMA step: 8 * nb.  Two additive codebooks keep nb <= 2 (16 tokens per z tile): at
+  // nb = 4 the second gather + add per fragment no longer fits the register budget and the kernel
+  // measured 6 x slower per token (o_proj 2x8: 11.8 us at 16 tokens, 75 us at 32; profiles/r2_22)
+  pl.nb = t <= 8 ? 1 : ((t <= 16 || m == 2) ? 2 : 4);
   const int tt = 8 * pl.nb;
   pl.z_tiles = (int)((t + tt - 1) / tt);
   const int t_tile = (int)(t < tt ? t : tt);

@@ -8,7 +8,11 @@
 // HBM.  A persistent, warp-specialised CTA per SM works on tiles of 128 weight rows x BN tokens:
 //   warp 0      TMA producer: x tile [BN tokens][64 k] bf16/fp16 -> shared memory (128-byte
 //               swizzle) with cp.async.bulk.tensor, completion on an mbarrier
-//   warps 4-7   dequant producers: one weight row per thread; per 64-wide k block they read
+//   warps 4-7, 12-15   two groups of dequant producers that take alternate code chunks (one or two
+//               64-wide k blocks), each filling its own pipeline stage: a group's k block is one
+//               serial chain (codes -> gathers -> stores -> proxy fence -> arrive) that a single warp
+//               per scheduler cannot hide (r1: ~1200 cycles per k block against 524 of MMA time);
+//               two groups overlap two chains.  One weight row per thread; per 64-wide k block they read
 //               the row's codes (8-16 B), gather the codewords (shared-memory codebooks, or L2
 //               for 65536-entry books), sum additive codebooks in fp32 with ONE rounding - the
 //               same bits pq_b200_dequant writes - and store them as the A operand in the
@@ -24,20 +28,23 @@
 // (BN = 16..64) still fill the 128-lane datapath.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <type_traits>
 
 #include "pq_common.cuh"
 
 namespace pq {
 
-constexpr int kTcThreads = 384;
+constexpr int kTcGroups = 2;               // dequant warp groups (4 warps each), alternating code chunks
+constexpr int kTcThreads = 384 + 128 * (kTcGroups - 1);
 constexpr int kTcBM = 128;                 // weight rows per tile = UMMA M
 constexpr int kTcBK = 64;                  // k per stage: 128 bytes = one swizzle atom
 constexpr int kTcMaxStages = 8;
 constexpr int kTcABytes = kTcBM * kTcBK * 2;
 constexpr int kTcTmemCols = 512;
+constexpr int kTcMaxSplit = 8;             // K splits of a few-tile problem
 constexpr int kTcCodeRing = 4;             // 16..64-byte code chunks in flight per dequant thread
-constexpr int kTcRingVec = 128 * 16;       // one 16-byte vector per dequant thread
+constexpr int kTcRingVec = 128 * kTcGroups * 16;   // one 16-byte vector per dequant thread
 
 struct TcArgs {
   const void* codes; const void* codebooks; const void* scales; const void* bias; void* y;
@@ -46,6 +53,12 @@ struct TcArgs {
   int BN;                                  // tokens per tile (UMMA N), multiple of 16
   int n_tok_tiles, n_row_tiles;
   int stages;
+  int groups;                              // dequant groups at work (1 or kTcGroups), see tc_plan
+  int ksplit;                              // CTAs along K per (token tile, row tile): few-tile problems (decode-sized
+                                           // batches on the small-N layers) otherwise leave most SMs idle
+  float* ws_part;                          // ksplit > 1: [ksplit][T][N] fp32 partial sums (workspace)
+  int* ws_tickets;                         // ksplit > 1: two counters per (token tile, row tile, epilogue warp); zero between launches
+  unsigned long long* trace;               // PQ_TC_TRACE builds: 16 stamps per CTA
   int cb_smem_bytes;                       // 0: gather codewords from global memory (L2)
   int cb_stride;                           // bytes between codebook entries as staged (128 when replicated)
   int row_code_bytes;                      // bytes of codes per weight row
@@ -218,6 +231,17 @@ __device__ __forceinline__ void tc_dequant_regs(uint32_t a_row, int r7, const ui
     for (int g = 0; g < GB; ++g) {
       if constexpr (M == 1) {
         tc_st_group<D>(a_row, r7, g0 + g, v[g][0]);
+      } else if constexpr (M == 2) {
+        // two codewords: the packed add IS the fp32 sum rounded once (a sum of two fp16 / bf16 values is
+        // exact in fp32) - the same bits as the general path, a fifth of its instructions
+        using T2 = typename Traits<T>::T2;
+        TcCw<D> o;
+#pragma unroll
+        for (int j = 0; j < D / 2; ++j) {
+          const T2 r2 = __hadd2(*reinterpret_cast<const T2*>(&v[g][0].w[j]), *reinterpret_cast<const T2*>(&v[g][1].w[j]));
+          o.w[j] = *reinterpret_cast<const uint32_t*>(&r2);
+        }
+        tc_st_group<D>(a_row, r7, g0 + g, o);
       } else {
         float acc[D];
 #pragma unroll
@@ -258,6 +282,15 @@ __device__ __forceinline__ void tc_dequant_generic(uint32_t a_row, int r7, const
   }
 }
 
+#ifdef PQ_TC_TRACE
+extern unsigned long long* g_lut_trace;
+#define TC_STAMP(buf, slot)                                                            \
+  do { if ((buf) != nullptr) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+       (buf)[blockIdx.x * 16 + (slot)] = t_; } } while (0)
+#else
+#define TC_STAMP(buf, slot) do {} while (0)
+#endif
+
 // ---- the kernel ---------------------------------------------------------------------------------
 // MT: codebooks per group known at compile time (1, 2, 4: codes prefetched through a per-thread
 // cp.async ring) or 0 (any M, codes read from global memory as needed).
@@ -269,6 +302,7 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) TC_STAMP(a.trace, 0);
   // dynamic shared memory: [A stages | B stages | codebooks], 1024-byte aligned tiles
   const uint32_t smem0 = (tc_smem_u32(tc_smem) + 1023u) & ~1023u;
   const uint32_t b_bytes = (uint32_t)a.BN * 128u;
@@ -298,20 +332,22 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  if (threadIdx.x == 0) TC_STAMP(a.trace, 1);
 
-  const int KB = a.K / kTcBK;
-  const int total_tiles = a.n_tok_tiles * a.n_row_tiles;
+  const int KB = a.K / kTcBK / a.ksplit;            // k blocks per tile (per K split)
+  const int tiles_per_split = a.n_tok_tiles * a.n_row_tiles;
+  const int total_tiles = tiles_per_split * a.ksplit;   // tile = (ks * n_tok_tiles + tt) * n_row_tiles + rt
 
   if (warp == 0) {
     // ===== TMA producer: x tiles =====
     if (lane == 0) {
       int s = 0; uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int tt = tile / a.n_row_tiles;
+        const int tt = (tile / a.n_row_tiles) % a.n_tok_tiles, kb0 = (tile / tiles_per_split) * KB;
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(empty(s), ph ^ 1u);
           mbar_arrive_expect_tx(full_b(s), b_bytes);
-          tma_load_2d(b_base + (uint32_t)s * b_bytes, &tmap_x, kb * kTcBK, tt * a.BN, full_b(s));
+          tma_load_2d(b_base + (uint32_t)s * b_bytes, &tmap_x, (kb0 + kb) * kTcBK, tt * a.BN, full_b(s));
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -327,7 +363,9 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
         const uint32_t d_tmem = tmem_base + (uint32_t)acc * 256u;
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(full_a(s), ph);
+          if (kb == 0) TC_STAMP(a.trace, 2);
           mbar_wait(full_b(s), ph);
+          if (kb == 0) TC_STAMP(a.trace, 3);
           tc_fence_after();
           const uint64_t ad = umma_desc_sw128(a_base + (uint32_t)s * kTcABytes);
           const uint64_t bd = umma_desc_sw128(b_base + (uint32_t)s * b_bytes);
@@ -338,38 +376,45 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
         umma_commit(tmem_full(acc));                 // accumulator complete
+        TC_STAMP(a.trace, 4);
         if (++acc == 2) { acc = 0; acc_ph ^= 1u; }
       }
     }
-  } else if (warp >= 4 && warp < 8) {
-    // ===== dequant producers: one weight row per thread =====
+  } else if ((warp >= 4 && warp < 8) || warp >= 12) {
+    // ===== dequant producers: one weight row per thread, group `grp` takes chunks grp, grp + G, ... =====
+    const int grp = warp >= 12 ? 1 + ((warp - 12) >> 2) : 0;
+    const int G = a.groups;
+    if (grp < G) {
     constexpr int GPB = kTcBK / D;
     constexpr int CBYTES = MT > 0 ? GPB * MT * (int)sizeof(CodeT) : 16;   // code bytes per row and k block
     constexpr int CHB = CBYTES > 16 ? CBYTES : 16;                         // ring chunk bytes per thread
     constexpr int CH = CHB / CBYTES;                                       // k blocks per chunk
     constexpr int NV = CHB / 16;
     constexpr int NW = CBYTES / 4;
-    const int r = threadIdx.x - 128;
+    const int r = (threadIdx.x & 127);               // 128-thread groups start at multiples of 128
     const int r7 = r & 7;
     const bool cb_in_smem = a.cb_smem_bytes > 0;
     const uint32_t cb_stride = (uint32_t)a.cb_stride;
     const int repl = a.cb_stride / (D * 2);          // copies of each entry in its 128-byte line (1: flat)
     const uint32_t lane_off = (uint32_t)(lane & (repl - 1)) * (D * 2);
     const size_t part_cb_bytes = (size_t)a.M * a.E * D * 2;
-    const uint32_t ring0 = tc_smem_u32(cb_smem + a.cb_smem_bytes) + (uint32_t)r * 16u;
+    const uint32_t ring0 = tc_smem_u32(cb_smem + a.cb_smem_bytes) + (uint32_t)(grp * 128 + r) * 16u;
     const int n_chunks = KB / CH;
+    const int gtid = grp * 128 + r;                  // index among all dequant threads
     int cur_part = -1;
-    int s = 0; uint32_t ph = 0;
 
-    // issue cursor of the code ring: runs kTcCodeRing chunks ahead of the consumer, across tiles
-    int itile = blockIdx.x, ichunk = 0, islot = 0;
+    // ---- issue cursor of the code ring: this group's chunks, kTcCodeRing ahead of the consumer.
+    // Chunks are numbered through the CTA's tiles; group g owns numbers g, g + G, g + 2G, ...
+    int itile = blockIdx.x, ichunk = grp, islot = 0;
     const unsigned char* irow = nullptr;
     auto seek = [&]() {
+      while (itile < total_tiles && ichunk >= n_chunks) { ichunk -= n_chunks; itile += gridDim.x; }
       irow = nullptr;
       if (itile < total_tiles) {
         const RowBlock rb = locate_row_block(a.parts, itile % a.n_row_tiles, kTcBM);
         if (rb.row0 + r < rb.row1)
-          irow = reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(rb.row0 + r) * a.row_code_bytes;
+          irow = reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(rb.row0 + r) * a.row_code_bytes +
+                 (size_t)(itile / tiles_per_split) * n_chunks * CHB;      // this K split's first chunk
       }
     };
     auto issue = [&]() {
@@ -382,7 +427,8 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
                            :: "r"(ring0 + (uint32_t)((islot * NV + v) * kTcRingVec)),
                               "l"(irow + (size_t)ichunk * CHB + 16 * v) : "memory");
           }
-          if (++ichunk == n_chunks) { ichunk = 0; itile += gridDim.x; seek(); }
+          ichunk += G;
+          if (ichunk >= n_chunks) seek();
           islot = (islot + 1 == kTcCodeRing) ? 0 : islot + 1;
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
@@ -393,68 +439,90 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
     for (int j = 0; j < kTcCodeRing; ++j) issue();
     int cslot = 0;
 
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    // ---- consumer: walk every tile of this CTA (all groups meet at the codebook reloads), dequantise
+    // this group's chunks.  (s, ph) is the pipeline stage of k block `cur`, counted through the tiles.
+    int s = 0; uint32_t ph = 0; int cur = 0;
+    int ch = grp, tile_k0 = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, tile_k0 += KB) {
       const int rt = tile % a.n_row_tiles;
       const RowBlock rb = locate_row_block(a.parts, rt, kTcBM);
       const int row = rb.row0 + r;
       const bool valid = row < rb.row1;
       const unsigned char* cb_g = reinterpret_cast<const unsigned char*>(a.codebooks) + (size_t)rb.part * part_cb_bytes;
       if (cb_in_smem && rb.part != cur_part) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");       // everyone is done with the old books
-        for (int e = r; e < a.M * a.E; e += 128) {           // entry e -> `repl` copies in its line
-          const TcCw<D> v = tc_ld_cw<D>(cb_g + (size_t)e * (D * 2), false);
-          for (int c = 0; c < repl; ++c) {
-            uint32_t* dst = reinterpret_cast<uint32_t*>(cb_smem + (size_t)e * cb_stride + c * (D * 2));
+        asm volatile("bar.sync 1, %0;" :: "r"(128 * G) : "memory");            // everyone is done with the old books
+        // one 16-byte slot of the staged books per thread and step: slot i holds entry i / repl (its
+        // `repl` copies are neighbours), so a warp writes 512 consecutive bytes.  (One thread per
+        // ENTRY, writing its copies word by word at a 128-byte stride, was a 32-way bank conflict on
+        // every store: 4.5 us for 256 entries, 10 us for 512 - most of a decode-sized launch; r2_24.)
+        for (int i = gtid; i < a.M * a.E * repl; i += 128 * G) {
+          const TcCw<D> v = tc_ld_cw<D>(cb_g + (size_t)(i / repl) * (D * 2), false);
+          uint32_t* dst = reinterpret_cast<uint32_t*>(cb_smem + (size_t)i * (D * 2));
+          if constexpr (D == 8) {
+            *reinterpret_cast<uint4*>(dst) = make_uint4(v.w[0], v.w[1], v.w[2], v.w[3]);
+          } else {
 #pragma unroll
             for (int j = 0; j < D / 2; ++j) dst[j] = v.w[j];
           }
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        asm volatile("bar.sync 1, %0;" :: "r"(128 * G) : "memory");
         cur_part = rb.part;
+        if (gtid == 0) TC_STAMP(a.trace, 7);
       }
       const unsigned char* cb = (cb_in_smem ? cb_smem : cb_g) + lane_off;
       const CodeT* crow = reinterpret_cast<const CodeT*>(
-          reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(valid ? row : rb.row0) * a.row_code_bytes);
-      for (int kb = 0; kb < KB; ++kb) {
-        uint32_t cw[NW];
-        if constexpr (MT > 0) {
-          const int sub = kb & (CH - 1);
-          if (sub == 0) asm volatile("cp.async.wait_group %0;" :: "n"(kTcCodeRing - 1) : "memory");
-          if (valid) {
-            if constexpr (CBYTES >= 16) {
+          reinterpret_cast<const unsigned char*>(a.codes) + (size_t)(valid ? row : rb.row0) * a.row_code_bytes) +
+          (size_t)(tile / tiles_per_split) * KB * GPB * a.M;              // this K split's first code
+      for (; ch < n_chunks; ch += G) {
+        {                                              // move the stage cursor to this chunk's first k block
+          s += tile_k0 + ch * CH - cur;
+          cur = tile_k0 + ch * CH;
+          while (s >= a.stages) { s -= a.stages; ph ^= 1u; }
+        }
+        if constexpr (MT > 0) asm volatile("cp.async.wait_group %0;" :: "n"(kTcCodeRing - 1) : "memory");
 #pragma unroll
-              for (int v = 0; v < NV; ++v)
-                asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
-                             : "=r"(cw[4 * v]), "=r"(cw[4 * v + 1]), "=r"(cw[4 * v + 2]), "=r"(cw[4 * v + 3])
-                             : "r"(ring0 + (uint32_t)((cslot * NV + v) * kTcRingVec)));
-            } else if constexpr (CBYTES == 8) {
-              asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(cw[0]), "=r"(cw[1])
-                           : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 8)));
-            } else {
-              asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cw[0]) : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 4)));
+        for (int sub = 0; sub < CH; ++sub) {
+          const int kb = ch * CH + sub;
+          uint32_t cw[NW];
+          if constexpr (MT > 0) {
+            if (valid) {
+              if constexpr (CBYTES >= 16) {
+#pragma unroll
+                for (int v = 0; v < NV; ++v)
+                  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                               : "=r"(cw[4 * v]), "=r"(cw[4 * v + 1]), "=r"(cw[4 * v + 2]), "=r"(cw[4 * v + 3])
+                               : "r"(ring0 + (uint32_t)((cslot * NV + v) * kTcRingVec)));
+              } else if constexpr (CBYTES == 8) {
+                asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(cw[0]), "=r"(cw[1])
+                             : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 8)));
+              } else {
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(cw[0]) : "r"(ring0 + (uint32_t)(cslot * kTcRingVec + sub * 4)));
+              }
             }
           }
+          mbar_wait(empty(s), ph ^ 1u);
+          const uint32_t a_row = a_base + (uint32_t)s * kTcABytes + (uint32_t)r * 128u;
+          if (!valid) tc_zero_block<D>(a_row, r7);
+          else if constexpr (MT > 0) tc_dequant_regs<T, D, CodeT, (MT > 0 ? MT : 1)>(a_row, r7, cw, a.E, cb, cb_stride, cb_in_smem);
+          else tc_dequant_generic<T, D, CodeT>(a_row, r7, crow + (size_t)kb * GPB * a.M, a.M, a.E, cb, cb_stride, cb_in_smem);
+          fence_proxy_async();                         // generic-proxy stores -> visible to the tensor core
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full_a(s));
+          if (gtid == 0 && cur == 0) TC_STAMP(a.trace, 8);
+          ++cur;
+          if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
-        mbar_wait(empty(s), ph ^ 1u);
-        const uint32_t a_row = a_base + (uint32_t)s * kTcABytes + (uint32_t)r * 128u;
-        if (!valid) tc_zero_block<D>(a_row, r7);
-        else if constexpr (MT > 0) tc_dequant_regs<T, D, CodeT, (MT > 0 ? MT : 1)>(a_row, r7, cw, a.E, cb, cb_stride, cb_in_smem);
-        else tc_dequant_generic<T, D, CodeT>(a_row, r7, crow + (size_t)kb * GPB * a.M, a.M, a.E, cb, cb_stride, cb_in_smem);
-        fence_proxy_async();                         // generic-proxy stores -> visible to the tensor core
-        __syncwarp();
-        if (lane == 0) mbar_arrive(full_a(s));
-        if (++s == a.stages) { s = 0; ph ^= 1u; }
-        if constexpr (MT > 0) {
-          if ((kb & (CH - 1)) == CH - 1) { issue(); cslot = (cslot + 1 == kTcCodeRing) ? 0 : cslot + 1; }
-        }
+        if constexpr (MT > 0) { issue(); cslot = (cslot + 1 == kTcCodeRing) ? 0 : cslot + 1; }
       }
+      ch -= n_chunks;                                  // this group's first chunk of the next tile
     }
+    }  // grp < G
   } else if (warp >= 8) {
     // ===== epilogue: TMEM -> registers -> y =====
     const int w = warp - 8;                          // == warp % 4: the TMEM lanes this warp may read
     int acc = 0; uint32_t acc_ph = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-      const int tt = tile / a.n_row_tiles, rt = tile % a.n_row_tiles;
+      const int rt = tile % a.n_row_tiles, tt = (tile / a.n_row_tiles) % a.n_tok_tiles, ks = tile / tiles_per_split;
       const RowBlock rb = locate_row_block(a.parts, rt, kTcBM);
       const int row = rb.row0 + 32 * w + lane;
       const bool valid = row < rb.row1;
@@ -464,19 +532,74 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
         if (a.bias) bi = Traits<T>::to_f(reinterpret_cast<const T*>(a.bias)[row]);
       }
       mbar_wait(tmem_full(acc), acc_ph);
+      if (w == 0 && lane == 0) TC_STAMP(a.trace, 5);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t)acc * 256u + ((uint32_t)(32 * w) << 16);
       T* yrow = reinterpret_cast<T*>(a.y) + row;
-      for (int c0 = 0; c0 < a.BN; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_x32(taddr + (uint32_t)c0, v);
+      if (a.ksplit == 1) {
+        for (int c0 = 0; c0 < a.BN; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_x32(taddr + (uint32_t)c0, v);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int tok = tt * a.BN + c0 + j;
-          if (valid && c0 + j < a.BN && tok < a.T)
-            yrow[(size_t)tok * a.y_stride] = Traits<T>::from_f(fmaf(__uint_as_float(v[j]), sc, bi));
+          for (int j = 0; j < 32; ++j) {
+            const int tok = tt * a.BN + c0 + j;
+            if (valid && c0 + j < a.BN && tok < a.T)
+              yrow[(size_t)tok * a.y_stride] = Traits<T>::from_f(fmaf(__uint_as_float(v[j]), sc, bi));
+          }
         }
+      } else {
+        // split K: this CTA's fp32 partial sums go to the workspace (lanes = 32 consecutive rows: one
+        // 128-byte line per token)
+        float* part = a.ws_part + (size_t)ks * a.T * a.N + row;
+        for (int c0 = 0; c0 < a.BN; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld_x32(taddr + (uint32_t)c0, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int tok = tt * a.BN + c0 + j;
+            if (valid && c0 + j < a.BN && tok < a.T) __stcg(part + (size_t)tok * a.N, __uint_as_float(v[j]));
+          }
+        }
+        __threadfence();
+        __syncwarp();
+        // All `ksplit` CTAs of a tile are resident at once (split launches have one tile per CTA and at
+        // most one CTA per SM), so they can wait for each other: a ticket counts arrivals, every
+        // split then reduces ITS share of the tile's tokens - ksplit warps add and store in parallel
+        // instead of the last arriver doing all of it (that serial tail was 15 us at 32 tokens, r2_24).
+        // The partials are added in split order: deterministic.  The last to leave zeroes the counters.
+        int* ticket = a.ws_tickets + (((size_t)tt * a.n_row_tiles + rt) * 4 + w) * 2;
+        if (lane == 0) {
+          atomicAdd(ticket, 1);
+          while (*reinterpret_cast<volatile int*>(ticket) < a.ksplit) {}
+        }
+        __syncwarp();
+        __threadfence();
+        const int per = (a.BN + a.ksplit - 1) / a.ksplit;
+        const int j_end = min(a.BN, (ks + 1) * per);
+        for (int j0 = ks * per; j0 < j_end; j0 += 8) {
+          float pv[kTcMaxSplit][8];
+#pragma unroll
+          for (int q = 0; q < kTcMaxSplit; ++q)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int tok = tt * a.BN + j0 + j;
+              pv[q][j] = (q < a.ksplit && valid && j0 + j < j_end && tok < a.T)
+                             ? __ldcg(a.ws_part + ((size_t)q * a.T + tok) * a.N + row) : 0.f;
+            }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int tok = tt * a.BN + j0 + j;
+            float sum = 0.f;
+#pragma unroll
+            for (int q = 0; q < kTcMaxSplit; ++q) sum += pv[q][j];        // split order; absent splits add 0
+            if (valid && j0 + j < j_end && tok < a.T)
+              yrow[(size_t)tok * a.y_stride] = Traits<T>::from_f(fmaf(sum, sc, bi));
+          }
+        }
+        __syncwarp();
+        if (lane == 0 && atomicAdd(ticket + 1, 1) == a.ksplit - 1) { ticket[0] = 0; ticket[1] = 0; }
       }
+      if (w == 0 && lane == 0) TC_STAMP(a.trace, 6);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tmem_empty(acc));
@@ -486,6 +609,7 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
 
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TC_STAMP(a.trace, 9);
   if (warp == 2) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "n"(kTcTmemCols) : "memory");
@@ -526,7 +650,7 @@ static int make_x_tmap(CUtensorMap* map, const void* x, int64_t x_stride, int64_
   return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
 }
 
-struct TcPlan { int bn, n_tok_tiles, stages, cb_smem, cb_stride, mt, ring_bytes, smem_total; };
+struct TcPlan { int bn, n_tok_tiles, stages, groups, cb_smem, cb_stride, mt, ring_bytes, smem_total, ch; };
 
 static bool tc_plan(TcPlan& pl, int64_t t, int64_t k, int d, int nbits, int m) {
   const int tok_tiles = (int)((t + 255) / 256);
@@ -545,12 +669,20 @@ static bool tc_plan(TcPlan& pl, int64_t t, int64_t k, int d, int nbits, int m) {
   const int64_t row_bytes = k / d * m * code_bytes;
   const int cbytes = kTcBK / d * m * code_bytes;
   pl.mt = ((m == 1 || m == 2 || m == 4) && row_bytes % 16 == 0 && cbytes <= 64) ? m : 0;
-  pl.ring_bytes = pl.mt ? kTcCodeRing * (cbytes > 16 ? cbytes : 16) * 128 : 0;
+  pl.ring_bytes = pl.mt ? kTcCodeRing * (cbytes > 16 ? cbytes : 16) * 128 * kTcGroups : 0;
   const int stage = kTcABytes + bn * 128;
   int stages = (int)((225 * 1024 - 1024 - pl.cb_smem - pl.ring_bytes) / stage);
   if (stages > kTcMaxStages) stages = kTcMaxStages;
   if (stages > k / kTcBK) stages = (int)(k / kTcBK) < 2 ? 2 : (int)(k / kTcBK);
   pl.stages = stages;
+  // Two dequant groups take alternate chunks of CH k blocks.  A group's consecutive k blocks are then up
+  // to (G - 1) * CH + 1 apart; the mbarrier parity wait on a stage is only unambiguous if that gap does
+  // not exceed the ring depth (a waiter may never be two phases ahead), else one group works alone.
+  const int ch = pl.mt ? ((cbytes > 16 ? cbytes : 16) / cbytes) : 1;
+  static const int force_groups = [] { const char* e = getenv("PQ_TC_GROUPS"); return e ? atoi(e) : 0; }();
+  pl.ch = ch;
+  pl.groups = ((kTcGroups - 1) * ch + 1 <= stages) ? kTcGroups : 1;
+  if (force_groups == 1) pl.groups = 1;
   pl.smem_total = stages * stage + pl.cb_smem + pl.ring_bytes + 1024;
   return stages >= 2;
 }
@@ -563,7 +695,25 @@ bool gemm_tc_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m)
   return tc_plan(pl, t, k, d, nbits, m);
 }
 
-int64_t gemm_tc_workspace(int64_t, int64_t, int64_t, int, int, int, int) { return 0; }
+constexpr int kTcTicketBytes = 64 * 1024;          // head of the workspace (include/pq_b200.h), shared with the table GEMV
+
+// K splits for problems with few tiles: the largest split <= SMs / tiles that keeps whole code chunks
+// and at least four k blocks per CTA.
+static int tc_ksplit(const TcPlan& pl, int64_t tiles, int64_t k) {
+  static const int force = [] { const char* e = getenv("PQ_TC_KSPLIT"); return e ? atoi(e) : 0; }();
+  const int kb = (int)(k / kTcBK);
+  int best = 1;
+  for (int ks = 2; ks <= kTcMaxSplit; ++ks) {
+    if (kb % ks || (kb / ks) % pl.ch || kb / ks < 4) continue;
+    if (tiles * ks <= sm_count() && (!force || ks <= force)) best = ks;   // one tile per CTA: the splits wait for each other
+  }
+  return force == 1 ? 1 : best;
+}
+
+// Only decode-sized batches split K (a prefill has tiles to spare): tickets + kTcMaxSplit partial sums.
+int64_t gemm_tc_workspace(int64_t t, int64_t n, int64_t, int, int, int, int) {
+  return t <= 256 ? kTcTicketBytes + (int64_t)kTcMaxSplit * t * n * 4 : 0;
+}
 
 template <typename T, int D, typename CodeT, int MT>
 static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, cudaStream_t stream) {
@@ -576,7 +726,7 @@ static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, 
     if (e != cudaSuccess) return (int)e;
     attr_set[dev & 63] = true;
   }
-  const int tiles = a.n_tok_tiles * a.n_row_tiles;
+  const int tiles = a.n_tok_tiles * a.n_row_tiles * a.ksplit;
   const int grid = tiles < sm_count() ? tiles : sm_count();
   kern<<<grid, kTcThreads, pl.smem_total, stream>>>(map, a);
   return (int)cudaGetLastError();
@@ -603,18 +753,30 @@ int gemm_tc_dispatch(const void* x, int64_t x_stride, const void* codes, const v
                      const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
                      int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
                      int n_parts, int dtype, void* workspace, int64_t workspace_bytes, cudaStream_t stream) {
-  (void)workspace; (void)workspace_bytes;
   if ((uintptr_t)x % 16 || (x_stride * 2) % 16 || (uintptr_t)codes % 16) return PQ_ERR_ALIGN;
   TcPlan pl;
   if (!tc_plan(pl, t, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
   TcArgs a{};
   a.codes = codes; a.codebooks = codebooks; a.scales = scales; a.bias = bias; a.y = y; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
-  a.BN = pl.bn; a.n_tok_tiles = pl.n_tok_tiles; a.stages = pl.stages; a.cb_smem_bytes = pl.cb_smem; a.cb_stride = pl.cb_stride;
+  a.BN = pl.bn; a.n_tok_tiles = pl.n_tok_tiles; a.stages = pl.stages; a.groups = pl.groups; a.cb_smem_bytes = pl.cb_smem; a.cb_stride = pl.cb_stride;
   a.row_code_bytes = (int)(k / d * m * (nbits <= 8 ? 1 : 2));
   int rc = make_parts(a.parts, part_sizes, n_parts, n, kTcBM);
   if (rc) return rc;
   a.n_row_tiles = a.parts.cta_end[n_parts - 1];
+#ifdef PQ_TC_TRACE
+  a.trace = g_lut_trace;
+#endif
+  a.ksplit = 1;
+  const int64_t tiles = (int64_t)a.n_tok_tiles * a.n_row_tiles;
+  if (workspace && t <= 256 && tiles * 4 * 2 * 4 <= kTcTicketBytes) {
+    const int ks = tc_ksplit(pl, tiles, k);
+    if (ks > 1 && workspace_bytes >= kTcTicketBytes + (int64_t)ks * t * n * 4) {
+      a.ksplit = ks;
+      a.ws_tickets = reinterpret_cast<int*>(workspace);
+      a.ws_part = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + kTcTicketBytes);
+    }
+  }
   CUtensorMap map;
   rc = make_x_tmap(&map, x, x_stride, t, k, pl.bn, dtype);
   if (rc) return rc;
