@@ -137,6 +137,15 @@ PQ_API int64_t pq_b200_gemm_silu_mul_workspace_bytes(int algo, int64_t t, int64_
 PQ_API int pq_b200_silu_and_mul(const void* x, int64_t x_stride, void* out, int64_t out_stride, int64_t t,
                                 int64_t k, int dtype, void* stream);
 
+/* out[i, :] = row ids[i] of the scaled dequantised [n, k] weight (one output partition): the embedding
+ * lookup of a PQ-quantised VocabParallelEmbedding  <- QuantizeMethodBase.embedding
+ * (vllm/model_executor/layers/quantization/base_config.py:30-35, layers/vocab_parallel_embedding.py:41-43,
+ * 229-246,395-404).  Bit-identical to the rows of pq_b200_dequant with scales.  ids: int64 on the device;
+ * an id outside [0, n) gives a zero row.  d in {4, 8, 16}.  Alignment: codebooks, out 16 bytes. */
+PQ_API int pq_b200_embedding(const int64_t* ids, int64_t n_ids, const void* codes, const void* codebooks,
+                             const void* scales, void* out, int64_t out_stride, int64_t n, int64_t k, int d,
+                             int nbits, int m, int dtype, void* stream);
+
 /* ---- fused epilogue / prologue of the decode table GEMV ------------------------
  * What the reference runs as separate launches around a row-parallel linear at decode
  *   apply -> tensor_model_parallel_all_reduce -> fused_add_rms_norm -> next linear

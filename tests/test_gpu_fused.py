@@ -174,3 +174,52 @@ def test_padded_codes_copy(k, fmt):
     w = lin.quant_method.dequantize(lin, scaled=True)
     w_ref = O.dequantize_partitions(c["codes"], c["codebooks"], [4096], c["scales"])
     assert torch.equal(w.cpu().view(torch.int16), w_ref.view(torch.int16))
+
+
+# ---- PQ vocabulary layers -----------------------------------------------------------
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2), (16, 8, 1), (4, 4, 1), (12, 16, 2)])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_embedding_rows_bit_exact(fmt, dtype):
+    b, d, m = fmt
+    vocab, hidden = 1000, 512
+    cfg = P.PQConfig(d, b, m, 1, lm_head_quantized=True)
+    c = O.make_case([vocab], hidden, b, d, m, dtype=dtype, seed=51)
+    with torch.device("cuda"):
+        emb = P.VocabParallelEmbedding(vocab, hidden, params_dtype=dtype, quant_config=cfg)
+    for name in ("codes", "codebooks", "scales"):
+        p = getattr(emb, name)
+        p.weight_loader(p, c[name].cuda())
+    ids = torch.tensor([[0, 999, 17, 17], [512, 1, 1000, 1023]], device="cuda")     # 1000, 1023: padding rows
+    out = emb(ids)
+    assert out.shape == (2, 4, hidden) and out.dtype == dtype
+    w_ref = O.dequantize_partitions(c["codes"], c["codebooks"], [vocab], c["scales"])
+    want = torch.zeros(2, 4, hidden, dtype=dtype)
+    for i in range(2):
+        for j in range(4):
+            if int(ids[i, j]) < vocab:
+                want[i, j] = w_ref[int(ids[i, j])]
+    real = (ids < vocab).cpu()
+    assert torch.equal(out.cpu()[real].view(torch.int16), want[real].view(torch.int16))
+    assert float(out.cpu()[~real].abs().max()) == 0.0        # padding rows: zero scale (+-0 either way)
+    # and it is the row gather of this library's own dequant
+    w = emb.quant_method.dequantize(emb, scaled=True)
+    assert torch.equal(out, w[ids])
+    # out-of-range ids (other shards' tokens under TP) give zero rows
+    z = P.ops.pq_embedding(torch.tensor([-1, 5000], device="cuda"), emb.codes, emb.codebooks, emb.scales)
+    assert float(z.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("t", [1, 5, 40])
+def test_lm_head_logits(t):
+    """Llama-2 vocabulary (32000 x 4096) as a PQ lm_head: logits against the oracle on a row sample."""
+    from tests.test_gpu_configs import check_sampled
+    cfg = P.PQConfig(8, 8, 1, 1, lm_head_quantized=True)
+    c = O.make_case([32000], 4096, 8, 8, 1, t=t, dtype=torch.float16, seed=52)
+    with torch.device("cuda"):
+        head = P.ParallelLMHead(32000, 4096, params_dtype=torch.float16, quant_config=cfg)
+    for name in ("codes", "codebooks", "scales"):
+        p = getattr(head, name)
+        p.weight_loader(p, c[name].cuda())
+    logits = head.compute_logits(c["x"].cuda())
+    assert logits.shape == (t, 32000)
+    check_sampled(logits, c, "lm_head")

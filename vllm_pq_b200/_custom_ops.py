@@ -38,6 +38,7 @@ _LIBRARY.define("gemm_fused(Tensor input, Tensor codes, Tensor codebooks, Tensor
                 "Tensor? norm_weight, float norm_eps, bool allreduce, bool silu_mul, bool want_ssq, "
                 "Tensor? codes_padded) -> (Tensor, Tensor)")
 _LIBRARY.define("fused_add_rms_norm(Tensor(a!) input, Tensor(b!)? residual, Tensor weight, float epsilon) -> ()")
+_LIBRARY.define("embedding(Tensor ids, Tensor codes, Tensor codebooks, Tensor scales) -> Tensor")
 _LIBRARY.define("dequant(Tensor codes, Tensor codebooks, int[] codebook_partition_sizes) -> Tensor")
 _LIBRARY.define("dequant_scaled(Tensor codes, Tensor codebooks, Tensor scales, "
                 "int[] codebook_partition_sizes) -> Tensor")
@@ -262,6 +263,24 @@ def _fused_add_rms_norm_cuda(input, residual, weight, epsilon):
         _lib.check(rc, "pq::fused_add_rms_norm")
 
 
+def _embedding_cuda(ids, codes, codebooks, scales):
+    _require_cuda(codes)
+    lib = _lib.load()
+    parts, n, g, m, d, nbits = _format(codes, codebooks, [])
+    if ids.dtype != torch.int64 or not ids.is_cuda:
+        raise RuntimeError("PQ: embedding ids must be an int64 CUDA tensor")
+    if scales.dtype != codebooks.dtype or scales.numel() != n or not scales.is_contiguous():
+        raise RuntimeError("PQ: scales must be contiguous [N,1,1,1] of the codebook dtype")
+    flat = ids.reshape(-1).contiguous()
+    out = torch.empty((flat.numel(), g * d), dtype=codebooks.dtype, device=codebooks.device)
+    with torch.cuda.device(codes.device):
+        rc = lib.pq_b200_embedding(flat.data_ptr(), flat.numel(), codes.data_ptr(), codebooks.data_ptr(),
+                                   scales.data_ptr(), out.data_ptr(), g * d, n, g * d, d, nbits, m,
+                                   _DTYPES[codebooks.dtype], torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "pq::embedding")
+    return out.reshape(ids.shape + (g * d,))
+
+
 def _gemm_cuda(input, codes, codebooks, scales, codebook_partition_sizes, bias):
     return _gemm_impl(input, codes, codebooks, scales, codebook_partition_sizes, bias, _lib.ALGO_AUTO)
 
@@ -305,6 +324,7 @@ _LIBRARY.impl("gemm_silu_mul", _gemm_silu_mul_cuda, "CUDA")
 _LIBRARY.impl("silu_and_mul", _silu_and_mul_cuda, "CUDA")
 _LIBRARY.impl("gemm_fused", _gemm_fused_cuda, "CUDA")
 _LIBRARY.impl("fused_add_rms_norm", _fused_add_rms_norm_cuda, "CUDA")
+_LIBRARY.impl("embedding", _embedding_cuda, "CUDA")
 _LIBRARY.impl("dequant", _dequant_cuda, "CUDA")
 _LIBRARY.impl("dequant_scaled", _dequant_scaled_cuda, "CUDA")
 
@@ -351,6 +371,9 @@ def _gemm_fused_fake(input, codes, codebooks, scales, codebook_partition_sizes, 
 
 torch.library.register_fake("pq::gemm_fused")(_gemm_fused_fake)
 torch.library.register_fake("pq::fused_add_rms_norm")(lambda input, residual, weight, epsilon: None)
+torch.library.register_fake("pq::embedding")(
+    lambda ids, codes, codebooks, scales: torch.empty(ids.shape + (codes.size(1) * codebooks.size(3),),
+                                                      dtype=codebooks.dtype, device=codebooks.device))
 torch.library.register_fake("pq::dequant")(_dequant_fake)
 torch.library.register_fake("pq::dequant_scaled")(_dequant_scaled_fake)
 
@@ -394,6 +417,12 @@ def fused_add_rms_norm(input: torch.Tensor, residual: Optional[torch.Tensor], we
     """In place, as the reference's ops.fused_add_rms_norm / rms_norm (vllm/_custom_ops.py,
     csrc/layernorm_kernels.cu:17-98): residual += input; input = RMSNorm(residual) * weight."""
     torch.ops.pq.fused_add_rms_norm(input, residual, weight, epsilon)
+
+
+def pq_embedding(ids: torch.Tensor, codes: torch.Tensor, codebooks: torch.Tensor, scales: torch.Tensor) -> torch.Tensor:
+    """F.embedding(ids, W) over the PQ weight W (one output partition): rows of the scaled dequantised
+    weight, bit-identical to pq_dequant(..., scales)[ids]; ids outside [0, N) give zero rows."""
+    return torch.ops.pq.embedding(ids, codes, codebooks, scales)
 
 
 def pq_dequant(codes: torch.Tensor, codebooks: torch.Tensor,

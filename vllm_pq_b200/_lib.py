@@ -59,6 +59,8 @@ SIGNATURES = {
                                       c_int, c_int, c_void_p, c_int64, c_void_p]),
     "pq_b200_gemm_silu_mul_workspace_bytes": (c_int64, [c_int, c_int64, c_int64, c_int64, c_int, c_int, c_int,
                                                         c_int]),
+    "pq_b200_embedding": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64,
+                                  c_int, c_int, c_int, c_int, c_void_p]),
     "pq_b200_gemm_fused": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
                                    c_int, c_void_p, c_int64, c_void_p, ctypes.POINTER(Epilogue)]),

@@ -20,6 +20,8 @@ int gemv_lut2_dispatch(const void*, int64_t, const void*, const void*, const voi
                        void*, int64_t, int64_t, int64_t, int64_t, int, int, int, const int64_t*,
                        int, int, void*, int64_t, cudaStream_t, int xact, const pq_b200_epilogue_t* ep);
 int64_t gemv_lut2_grid_x(int64_t, int64_t, int64_t, int, int, int, const int64_t*, int, int64_t);
+int embedding_dispatch(const long long*, int64_t, const void*, const void*, const void*, void*, int64_t, int64_t,
+                       int64_t, int, int, int, int, cudaStream_t);
 int add_rms_norm_dispatch(void*, int64_t, void*, int64_t, const void*, float, int64_t, int64_t, int, cudaStream_t);
 int silu_and_mul_dispatch(const void*, int64_t, void*, int64_t, int64_t, int64_t, int, cudaStream_t);
 int64_t gemv_lut2_workspace(int64_t t, int64_t n, int64_t k, int d, int nbits, int m, int n_parts);
@@ -299,6 +301,21 @@ int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, int nbi
   if (check_format(n, k, d, nbits, m, part_sizes, n_parts, PQ_F16)) return PQ_ERR_SHAPE;
   if (!pq::gemv_lut2_fused_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
   return pq::gemv_lut2_grid_x(t, n, k, d, nbits, m, part_sizes, n_parts, workspace_bytes);
+}
+
+int pq_b200_embedding(const int64_t* ids, int64_t n_ids, const void* codes, const void* codebooks, const void* scales,
+                      void* out, int64_t out_stride, int64_t n, int64_t k, int d, int nbits, int m, int dtype,
+                      void* stream) {
+  const int64_t one = n;
+  int rc = check_format(n, k, d, nbits, m, &one, 1, dtype);
+  if (rc) return rc;
+  if (!ids || !codes || !codebooks || !scales || !out) return PQ_ERR_NULL;
+  if (n_ids < 0 || out_stride < k) return PQ_ERR_SHAPE;
+  if (d != 4 && d != 8 && d != 16) return PQ_ERR_FORMAT;
+  if ((((uintptr_t)codebooks | (uintptr_t)out) & 15) || (out_stride * 2) % 16) return PQ_ERR_ALIGN;
+  if (n_ids == 0) return PQ_OK;
+  return pq::embedding_dispatch(reinterpret_cast<const long long*>(ids), n_ids, codes, codebooks, scales, out,
+                                out_stride, n, k, d, nbits, m, dtype, (cudaStream_t)stream);
 }
 
 int pq_b200_fused_add_rms_norm(void* input, int64_t input_stride, void* residual, int64_t residual_stride,

@@ -238,4 +238,79 @@ int dequant_dispatch(const void* codes, const void* codebooks, const void* scale
       : launch_dequant_t<__nv_bfloat16, uint16_t>(codes, codebooks, scales, out, n, k, d, m, E, part_sizes, n_parts, stream);
 }
 
+// ---- embedding lookup over PQ weights ----------------------------------------
+// out[i, :] = scaled dequantised row ids[i] of a [n, k] PQ matrix - what QuantizeMethodBase.embedding
+// has to return for a quantised VocabParallelEmbedding (base_config.py:30-35,
+// vocab_parallel_embedding.py:41-43,229-246: F.embedding over the weight).  The same bits as the
+// corresponding row of pq_b200_dequant with scales (fp32 sum over the M codewords, one rounding,
+// scale multiply rounded once more: aqlm.py:60-72).  Ids outside [0, n) give a zero row (the caller
+// masks the ids of other vocabulary shards, vocab_parallel_embedding.py:395-404).  One CTA per id,
+// one group per thread; codewords come straight from global memory / L2: a decode step looks up
+// a handful of rows, staging a codebook in shared memory would cost more than it saves.
+template <typename T, int D, typename CodeT>
+__global__ void __launch_bounds__(256)
+pq_embedding_kernel(const long long* __restrict__ ids, const CodeT* __restrict__ codes, const T* __restrict__ codebooks,
+                    const T* __restrict__ scales, T* __restrict__ out, long long out_stride, int n, int G, int M, int E) {
+  const long long id = ids[blockIdx.x];
+  T* o = out + (size_t)blockIdx.x * out_stride;
+  const bool ok = id >= 0 && id < n;
+  const uint32_t emask = (uint32_t)E - 1u;
+  const float sc = ok ? Traits<T>::to_f(scales[id]) : 0.f;
+  for (int g = threadIdx.x; g < G; g += 256) {
+    WVec<D> r;
+#pragma unroll
+    for (int j = 0; j < D / 2; ++j) r.w[j] = 0u;
+    if (ok) {
+      float acc[D];
+#pragma unroll
+      for (int j = 0; j < D; ++j) acc[j] = 0.f;
+      const CodeT* c = codes + ((size_t)id * G + g) * M;
+      for (int m = 0; m < M; ++m) {
+        const uint32_t code = (uint32_t)c[m] & emask;
+        const WVec<D> v = ld_entry_gmem<D>(reinterpret_cast<const uint32_t*>(codebooks) + ((size_t)m * E + code) * (D / 2));
+#pragma unroll
+        for (int j = 0; j < D / 2; ++j) {
+          const float2 f = Traits<T>::to_f2(v.w[j]);
+          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < D / 2; ++j) {
+        // round the sum (aqlm.py:60-65), then the scale multiply in the weight dtype (aqlm.py:70-72)
+        const float2 w = Traits<T>::to_f2(Traits<T>::pack(acc[2 * j], acc[2 * j + 1]));
+        r.w[j] = Traits<T>::pack(w.x * sc, w.y * sc);
+      }
+    }
+    st_group<D>(o + (size_t)g * D, r);
+  }
+}
+
+template <typename T, typename CodeT>
+static int launch_embedding(const long long* ids, int64_t n_ids, const void* codes, const void* codebooks,
+                            const void* scales, void* out, int64_t out_stride, int64_t n, int64_t k, int d, int nbits,
+                            int m, cudaStream_t stream) {
+  const int G = (int)(k / d), E = 1 << nbits;
+#define PQ_EMB(DD)                                                                                              \
+  pq_embedding_kernel<T, DD, CodeT><<<(unsigned)n_ids, 256, 0, stream>>>(                                       \
+      ids, (const CodeT*)codes, (const T*)codebooks, (const T*)scales, (T*)out, (long long)out_stride, (int)n, G, m, E)
+  switch (d) {
+    case 4: PQ_EMB(4); break;
+    case 8: PQ_EMB(8); break;
+    case 16: PQ_EMB(16); break;
+    default: return PQ_ERR_FORMAT;
+  }
+#undef PQ_EMB
+  return (int)cudaGetLastError();
+}
+
+int embedding_dispatch(const long long* ids, int64_t n_ids, const void* codes, const void* codebooks,
+                       const void* scales, void* out, int64_t out_stride, int64_t n, int64_t k, int d, int nbits,
+                       int m, int dtype, cudaStream_t stream) {
+  if (dtype == PQ_F16)
+    return nbits <= 8 ? launch_embedding<__half, uint8_t>(ids, n_ids, codes, codebooks, scales, out, out_stride, n, k, d, nbits, m, stream)
+                      : launch_embedding<__half, uint16_t>(ids, n_ids, codes, codebooks, scales, out, out_stride, n, k, d, nbits, m, stream);
+  return nbits <= 8 ? launch_embedding<__nv_bfloat16, uint8_t>(ids, n_ids, codes, codebooks, scales, out, out_stride, n, k, d, nbits, m, stream)
+                    : launch_embedding<__nv_bfloat16, uint16_t>(ids, n_ids, codes, codebooks, scales, out, out_stride, n, k, d, nbits, m, stream);
+}
+
 }  // namespace pq

@@ -49,10 +49,16 @@ class PQConfigBody:
     _config_base: type = object                              # set by make_classes
     _method_cls: type = None                                 # "
     _is_linear = staticmethod(lambda layer: False)           # "
+    _is_vocab = staticmethod(lambda layer: False)            # ": VocabParallelEmbedding / ParallelLMHead
 
     def __init__(self, in_group_size: int, nbits_per_codebook: int, num_codebooks: int,
-                 out_group_size: int = 1) -> None:
+                 out_group_size: int = 1, lm_head_quantized: bool = False) -> None:
         type(self)._config_base.__init__(self)
+        # The reference leaves embeddings and lm_head dense (aqlm.py:213-217 returns None for anything
+        # but a LinearBase).  With "lm_head_quantized": true in the HF quantization_config (the key
+        # vLLM's GPTQ / AWQ-marlin configs use for the same switch) the vocabulary layers take PQ
+        # weights too: SURVEY.md 8f N4.
+        self.lm_head_quantized = bool(lm_head_quantized)
         self.in_group_size = in_group_size
         self.nbits_per_codebook = nbits_per_codebook
         self.num_codebooks = num_codebooks
@@ -87,7 +93,8 @@ class PQConfigBody:
     @classmethod
     def from_config(cls, config: Dict[str, Any]) -> "PQConfig":
         return cls(_from_keys(config, "in_group_size"), _from_keys(config, "nbits_per_codebook"),
-                   _from_keys(config, "num_codebooks"), _from_keys(config, "out_group_size"))
+                   _from_keys(config, "num_codebooks"), _from_keys(config, "out_group_size"),
+                   bool(config.get("lm_head_quantized", False)))
 
     @classmethod
     def override_quantization_method(cls, hf_quant_cfg, user_quant) -> Optional[str]:
@@ -100,6 +107,8 @@ class PQConfigBody:
     def get_quant_method(self, layer: torch.nn.Module, prefix: str = "") -> Optional["PQLinearMethod"]:
         if type(self)._is_linear(layer):
             return type(self)._method_cls(self)
+        if self.lm_head_quantized and type(self)._is_vocab(layer):
+            return type(self)._method_cls(self)              # PQ lm_head / embedding (N4)
         return None                                          # embeddings / lm_head stay dense
 
 
@@ -252,6 +261,12 @@ class PQLinearMethodBody:
         rstd = torch.rsqrt(ssq.reshape(-1, ssq.shape[-1]).sum(-1, keepdim=True) / x.shape[-1] + eps)
         return ((x.reshape(-1, x.shape[-1]).float() * rstd).to(x.dtype) * weight).reshape(x.shape)
 
+    def embedding(self, layer: torch.nn.Module, input_: torch.Tensor) -> torch.Tensor:
+        """Rows ``input_`` of the scaled dequantised weight (QuantizeMethodBase.embedding,
+        base_config.py:30-35; UnquantizedEmbeddingMethod.embedding is F.embedding over the weight,
+        vocab_parallel_embedding.py:41-43).  Bit-identical to ``dequantize(layer)[input_]``."""
+        return ops.pq_embedding(input_, layer.codes, layer.codebooks, layer.scales)
+
     def dequantize(self, layer: torch.nn.Module, scaled: bool = True) -> torch.Tensor:
         """Dense [N, K] weight (aqlm.py:37-74); bit-exact with the reference."""
         codebooks = layer.codebooks
@@ -259,7 +274,7 @@ class PQLinearMethodBody:
         return ops.pq_dequant(layer.codes, codebooks, parts, layer.scales if scaled else None)
 
 
-def make_classes(config_base: type, method_base: type, is_linear, name: str = "pq"):
+def make_classes(config_base: type, method_base: type, is_linear, name: str = "pq", is_vocab=None):
     """(PQConfig, PQLinearMethod) as real subclasses of the given ABCs.  ``is_linear(layer)`` is the
     ``isinstance(layer, LinearBase)`` test of aqlm.py:213-217 for whichever LinearBase is in use."""
     method_cls = type("PQLinearMethod", (PQLinearMethodBody, method_base),
@@ -268,6 +283,7 @@ def make_classes(config_base: type, method_base: type, is_linear, name: str = "p
         "__doc__": "Config class for PQ (AQLM-format) checkpoints.  aqlm.py:159-217.",
         "__module__": __name__,
         "_config_base": config_base, "_method_cls": method_cls, "_is_linear": staticmethod(is_linear),
+        "_is_vocab": staticmethod(is_vocab if is_vocab is not None else (lambda layer: False)),
         "_registered_name": name,
     })
     return config_cls, method_cls
@@ -278,5 +294,10 @@ def _is_own_linear(layer) -> bool:
     return is_linear_layer(layer)
 
 
-PQConfig, PQLinearMethod = make_classes(QuantizationConfig, LinearMethodBase, _is_own_linear)
+def _is_own_vocab(layer) -> bool:
+    from .embedding import VocabParallelEmbedding
+    return isinstance(layer, VocabParallelEmbedding)
+
+
+PQConfig, PQLinearMethod = make_classes(QuantizationConfig, LinearMethodBase, _is_own_linear, is_vocab=_is_own_vocab)
 PQConfig = register_quantization_config("pq")(PQConfig)

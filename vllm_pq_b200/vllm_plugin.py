@@ -30,7 +30,10 @@ def register(name: str = "pq"):
 
     from .pq import make_classes
 
+    from vllm.model_executor.layers.vocab_parallel_embedding import VocabParallelEmbedding
+
     config_cls, _ = make_classes(QuantizationConfig, LinearMethodBase,
-                                 lambda layer: isinstance(layer, LinearBase), name)
+                                 lambda layer: isinstance(layer, LinearBase), name,
+                                 is_vocab=lambda layer: isinstance(layer, VocabParallelEmbedding))
     _REGISTERED = register_quantization_config(name)(config_cls)
     return _REGISTERED
