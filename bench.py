@@ -506,8 +506,11 @@ def run_gpu_arm(args):
                        "batch": B, "format": f"{b}bit x d{d} x M{m}", "parallelism": f"tp{world}",
                        "cold_l2": f"each step streams {model.code_bytes() * world / 1e6:.0f} MB of distinct codes (> 126 MB L2)",
                        "launch": ("CUDA graph" if use_graph else "eager") + (" + programmatic dependent launch" if args.pdl else ""),
-                       "allreduce": ("one-shot NVLink P2P kernel" if (world > 1 and P.distributed.oneshot_enabled())
-                                     else ("nccl" if world > 1 else "none")),
+                       "allreduce": ("none" if world == 1 else "nccl" if not P.distributed.oneshot_enabled() else
+                                     "fused into the row-parallel GEMV epilogue (NVLink peer memory, LL packets)"
+                                     if (B <= 8 and b == 8 and P.distributed.fused_allreduce_comm() is not None) else
+                                     "one-shot NVLink P2P kernel" if B * shape.hidden * 2 <= (1 << 20) else
+                                     "two-stage NVLink P2P kernel (reduce-scatter + all-gather)"),
                        "mlp_act": ("SiLU(gate)*up on down_proj's x load" if args.fused_act
                                    else "stand-in slice of gate_up (no activation math)")},
             "e2e": {"value": B / (ms_e2e * 1e-3), "unit": UNIT,

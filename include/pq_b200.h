@@ -227,6 +227,18 @@ PQ_API int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems,
                                      void* const* peer_data, void* const* peer_flags,
                                      int rank, int world, int64_t slot_bytes, void* stream);
 
+/* Two-stage all-reduce (reduce-scatter + all-gather over peer memory) for messages above the one-shot
+ * limit - the prefill partial sums of the row-parallel layers.  Replaces cross_device_reduce_2stage
+ * (custom_all_reduce.cuh:239-290,478-491) and, under CUDA-graph capture, the ctypes NCCL path of
+ * device_communicators/pynccl.py:109-132: one launch, device-side epoch, replayable.  Per rank (cudaMalloc'd,
+ * exchanged by CUDA IPC): peer_stage[r] max_bytes; peer_res[r] 2 * round_up(max_bytes / world, 256) bytes;
+ * peer_flags[r] PQ_AR2_FLAG_BYTES, zeroed once.  n_elems * 2 <= max_bytes, a multiple of 16; max_bytes a
+ * multiple of 256; world in {2, 4, 8}.  Bitwise identical results on every rank. */
+#define PQ_AR2_FLAG_BYTES 8192
+PQ_API int pq_b200_allreduce_twostage(const void* in, void* out, int64_t n_elems, int dtype,
+                                      void* const* peer_stage, void* const* peer_res, void* const* peer_flags,
+                                      int rank, int world, int64_t max_bytes, void* stream);
+
 /* Device buffers whose base address is what cudaIpcGetMemHandle maps (torch's caching
  * allocator sub-allocates, so its pointers cannot be shared this way), and the 64-byte
  * cudaIpcMemHandle_t exchange (reference: custom_all_reduce.py:178-201). */

@@ -33,7 +33,9 @@ def main():
 
     # ---- 1. one-shot all-reduce vs NCCL ----
     oneshot = P.distributed.oneshot_enabled()
-    for n in (4096, 8192, 64 * 4096):
+    # one-shot (<= 1 MiB), two-stage (<= 64 MiB: 2048 x 4096, 2048 x 8192, a size that does not divide
+    # into equal chunks) and NCCL (above)
+    for n in (4096, 8192, 64 * 4096, 2048 * 4096, 2048 * 8192, 1000 * 4096 + 8, (64 << 19) + 8):
         for dt in (torch.float16, torch.bfloat16):
             g = torch.Generator(device=dev).manual_seed(100 + rank)
             x = torch.randn(n, device=dev, dtype=dt, generator=g)
@@ -50,24 +52,25 @@ def main():
             if not (err <= tol) or not bitwise:
                 ok = False
                 print(f"[rank {rank}] allreduce n={n} {dt}: err={err:.2e} bitwise_equal_across_ranks={bitwise}")
-    # graph replay of the one-shot kernel (epoch counter lives on the device)
-    x = torch.randn(8192, device=dev, dtype=torch.float16)
-    s = torch.cuda.Stream()
-    with torch.cuda.stream(s):
-        P.tensor_model_parallel_all_reduce(x.clone())
-        s.synchronize()
-        dist.barrier()
-        gr = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(gr, stream=s):
-            y = P.tensor_model_parallel_all_reduce(x)
-    ref = x.float().clone()
-    dist.all_reduce(ref)
-    for _ in range(5):
-        gr.replay()
-    torch.cuda.synchronize()
-    if not (float((y.float() - ref).abs().max() / ref.abs().max()) <= 2e-3):
-        ok = False
-        print(f"[rank {rank}] graph-replayed all-reduce mismatch")
+    # graph replay of the one-shot and of the two-stage kernel (epoch counters live on the device)
+    for n_graph in (8192, 2048 * 8192):
+        x = torch.randn(n_graph, device=dev, dtype=torch.float16)
+        s = torch.cuda.Stream()
+        with torch.cuda.stream(s):
+            P.tensor_model_parallel_all_reduce(x.clone())
+            s.synchronize()
+            dist.barrier()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, stream=s):
+                y = P.tensor_model_parallel_all_reduce(x)
+        ref = x.float().clone()
+        dist.all_reduce(ref)
+        for _ in range(5):
+            gr.replay()
+        torch.cuda.synchronize()
+        if not (float((y.float() - ref).abs().max() / ref.abs().max()) <= 2e-3):
+            ok = False
+            print(f"[rank {rank}] graph-replayed all-reduce mismatch (n = {n_graph})")
 
     # ---- 2. TP decoder-layer linears against the ORACLE (fp64 contraction over the FULL tensors) ----
     # hidden 2048, intermediate 5632: at TP = 8 down_proj's shard has 88 code bytes per row (not a

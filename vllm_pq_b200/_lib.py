@@ -20,6 +20,7 @@ ALGO_NAMES = {0: "auto", 1: "gemv_direct", 2: "gemv_lut", 3: "gemm_tc", 4: "gemm
 ABI_VERSION = 2
 MAX_PARTS = 8
 AR_FLAG_BYTES = 4096
+AR2_FLAG_BYTES = 8192
 AR_MAX_WORLD = 8
 
 # every symbol include/pq_b200.h declares: (restype, argtypes)
@@ -73,6 +74,8 @@ SIGNATURES = {
     "pq_b200_pick_algo": (c_int, [c_int64, c_int64, c_int64, c_int, c_int, c_int]),
     "pq_b200_allreduce_oneshot": (c_int, [c_void_p, c_void_p, c_int64, c_int, _VPP, _VPP, c_int, c_int,
                                           c_int64, c_void_p]),
+    "pq_b200_allreduce_twostage": (c_int, [c_void_p, c_void_p, c_int64, c_int, _VPP, _VPP, _VPP, c_int, c_int,
+                                           c_int64, c_void_p]),
     "pq_b200_malloc": (c_int, [c_int64, _VPP]),
     "pq_b200_free": (c_int, [c_void_p]),
     "pq_b200_ipc_get_handle": (c_int, [c_void_p, c_void_p]),

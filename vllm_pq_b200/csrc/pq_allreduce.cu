@@ -136,6 +136,149 @@ static int launch_ar(const void* in, void* out, int n_vec, const ArPeers& peers,
   return rc;
 }
 
+// ---- two-stage all-reduce for messages above the one-shot limit (prefill: [T, hidden] partial sums) ----
+// Replaces cross_device_reduce_2stage (csrc/custom_all_reduce.cuh:239-290, dispatch :478-491) and, for
+// CUDA-graph capture, the ctypes NCCL binding the reference needs for large messages
+// (device_communicators/pynccl.py:109-132): one launch, no host state, epoch on the device.
+//   A  copy the input into this rank's peer-mapped staging buffer              (local)
+//      barrier 1 (per block: the element -> block map is the same on every rank)
+//   B  reduce-scatter: rank r sums chunk r of every rank's staging buffer in rank order, fp32, and
+//      writes the rounded chunk into its own result buffer                    (W - 1 remote reads)
+//      barrier 2
+//   C  all-gather: copy chunk q from rank q's result buffer into the output    (W - 1 remote reads)
+// Every rank adds the same fp32 values in the same order and every rank reads the same rounded
+// chunks: bitwise identical results across ranks.  The result buffer alternates by launch parity (a
+// fast rank may write launch n + 1's chunk while a slow one still gathers launch n's).
+constexpr int kAr2Threads = 512;
+constexpr int kAr2MaxBlocks = 128;
+constexpr int kAr2CounterWord = 2000;  // flag buffer: [block * world + peer] (<= 1024 words), then
+constexpr int kAr2TicketWord = 2001;   // this rank's epoch counter and block ticket
+
+struct Ar2Peers {
+  unsigned char* stage[PQ_AR_MAX_WORLD];   // [max_bytes] staging copies of the inputs
+  unsigned char* res[PQ_AR_MAX_WORLD];     // [2][max_bytes / world] reduced chunks, by launch parity
+  uint32_t* flags[PQ_AR_MAX_WORLD];
+};
+
+template <int WORLD>
+__device__ __forceinline__ void ar2_barrier(const Ar2Peers& peers, int rank, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < WORLD) {
+    __threadfence_system();
+    st_release_sys(peers.flags[threadIdx.x] + blockIdx.x * WORLD + rank, epoch);
+    while ((int32_t)(ld_acquire_sys(peers.flags[rank] + blockIdx.x * WORLD + threadIdx.x) - epoch) < 0) {}
+  }
+  __syncthreads();
+}
+
+template <typename T, int WORLD>
+__global__ void __launch_bounds__(kAr2Threads)
+pq_allreduce_twostage_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int n_vec, Ar2Peers peers,
+                             int rank, long long res_parity_bytes) {
+  pdl_launch_dependents();
+  pdl_wait();
+  uint32_t* my_flags = peers.flags[rank];
+  const uint32_t base = *reinterpret_cast<volatile uint32_t*>(my_flags + kAr2CounterWord);
+  const int chunk = (n_vec + WORLD - 1) / WORLD;                  // vectors per rank's chunk
+  const int per_block = (chunk + gridDim.x - 1) / gridDim.x;
+  const int i0 = blockIdx.x * per_block, i1 = min(i0 + per_block, chunk);
+  const long long parity_off = (long long)((base >> 1) & 1u) * res_parity_bytes;
+
+  // A: this block's slice of every chunk -> staging
+  uint4* my_stage = reinterpret_cast<uint4*>(peers.stage[rank]);
+#pragma unroll 1
+  for (int q = 0; q < WORLD; ++q)
+    for (int i = i0 + threadIdx.x; i < i1; i += kAr2Threads) {
+      const int v = q * chunk + i;
+      if (v < n_vec) my_stage[v] = in[v];
+    }
+  ar2_barrier<WORLD>(peers, rank, base + 1u);
+
+  // B: reduce chunk `rank`
+  uint4* my_res = reinterpret_cast<uint4*>(peers.res[rank] + parity_off);
+  for (int i = i0 + threadIdx.x; i < i1; i += kAr2Threads) {
+    const int v = rank * chunk + i;
+    if (v >= n_vec) continue;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int q = 0; q < WORLD; ++q) {
+      const uint4 val = ld_cg_16(reinterpret_cast<const uint4*>(peers.stage[q]) + v);
+      const uint32_t w[4] = {val.x, val.y, val.z, val.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = Traits<T>::to_f2(w[j]);
+        acc[2 * j] += f.x;
+        acc[2 * j + 1] += f.y;
+      }
+    }
+    my_res[i] = make_uint4(Traits<T>::pack(acc[0], acc[1]), Traits<T>::pack(acc[2], acc[3]),
+                           Traits<T>::pack(acc[4], acc[5]), Traits<T>::pack(acc[6], acc[7]));
+  }
+  ar2_barrier<WORLD>(peers, rank, base + 2u);
+
+  // C: gather every rank's reduced chunk
+#pragma unroll 1
+  for (int p = 0; p < WORLD; ++p) {
+    const int q = (rank + p) % WORLD;                               // spread the links
+    const uint4* src = reinterpret_cast<const uint4*>(peers.res[q] + parity_off);
+    for (int i = i0 + threadIdx.x; i < i1; i += kAr2Threads) {
+      const int v = q * chunk + i;
+      if (v < n_vec) out[v] = ld_cg_16(src + i);
+    }
+  }
+
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(my_flags + kAr2TicketWord, 1u);
+    if (done == gridDim.x - 1) {
+      my_flags[kAr2TicketWord] = 0u;
+      __threadfence();
+      *reinterpret_cast<volatile uint32_t*>(my_flags + kAr2CounterWord) = base + 2u;
+    }
+  }
+}
+
+int allreduce_twostage_dispatch(const void* in, void* out, int64_t n_elems, int dtype, void* const* peer_stage,
+                                void* const* peer_res, void* const* peer_flags, int rank, int world,
+                                int64_t max_bytes, cudaStream_t stream) {
+  Ar2Peers peers{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_stage[r] || !peer_res[r] || !peer_flags[r]) return PQ_ERR_NULL;
+    peers.stage[r] = (unsigned char*)peer_stage[r];
+    peers.res[r] = (unsigned char*)peer_res[r];
+    peers.flags[r] = (uint32_t*)peer_flags[r];
+  }
+  const int n_vec = (int)(n_elems * 2 / 16);
+  const int chunk = (n_vec + world - 1) / world;
+  int blocks = (chunk + kAr2Threads * 4 - 1) / (kAr2Threads * 4);       // >= 4 vectors per thread
+  if (blocks > kAr2MaxBlocks) blocks = kAr2MaxBlocks;
+  if (blocks < 1) blocks = 1;
+  const long long res_parity_bytes = ((max_bytes / world + 255) / 256) * 256;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(blocks); cfg.blockDim = dim3(kAr2Threads); cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = g_use_pdl ? 1 : 0;
+  int rc = 0;
+#define PQ_AR2(TT, W)                                                                              \
+  rc = (int)cudaLaunchKernelEx(&cfg, pq_allreduce_twostage_kernel<TT, W>, (const uint4*)in, (uint4*)out, \
+                               n_vec, peers, rank, res_parity_bytes)
+#define PQ_AR2_W(TT)                               \
+  switch (world) {                                  \
+    case 2: PQ_AR2(TT, 2); break;                   \
+    case 4: PQ_AR2(TT, 4); break;                   \
+    case 8: PQ_AR2(TT, 8); break;                   \
+    default: return PQ_ERR_UNSUPPORTED;             \
+  }
+  if (dtype == PQ_F16) { PQ_AR2_W(__half) } else { PQ_AR2_W(__nv_bfloat16) }
+#undef PQ_AR2_W
+#undef PQ_AR2
+  return rc;
+}
+
 int allreduce_oneshot_dispatch(const void* in, void* out, int64_t n_elems, int dtype,
                                void* const* peer_data, void* const* peer_flags, int rank, int world,
                                int64_t slot_bytes_in, cudaStream_t stream) {

@@ -39,6 +39,8 @@ int gemm_mma_dispatch(const void*, int64_t, const void*, const void*, const void
 bool gemm_mma_supported(int64_t t, int64_t n, int64_t k, int d, int nbits, int m);
 int allreduce_oneshot_dispatch(const void*, void*, int64_t, int, void* const*, void* const*, int, int,
                                int64_t, cudaStream_t);
+int allreduce_twostage_dispatch(const void*, void*, int64_t, int, void* const*, void* const*, void* const*, int, int,
+                                int64_t, cudaStream_t);
 extern bool g_use_pdl;
 extern unsigned long long* g_lut_trace;
 extern int g_lut_last_grid[4];
@@ -337,6 +339,18 @@ int pq_b200_allreduce_oneshot(const void* in, void* out, int64_t n_elems, int dt
   if (n_elems * 2 > slot_bytes) return PQ_ERR_WORKSPACE;
   return pq::allreduce_oneshot_dispatch(in, out, n_elems, dtype, peer_data, peer_flags, rank, world, slot_bytes,
                                         (cudaStream_t)stream);
+}
+
+int pq_b200_allreduce_twostage(const void* in, void* out, int64_t n_elems, int dtype, void* const* peer_stage,
+                               void* const* peer_res, void* const* peer_flags, int rank, int world,
+                               int64_t max_bytes, void* stream) {
+  if (dtype != PQ_F16 && dtype != PQ_BF16) return PQ_ERR_DTYPE;
+  if (!in || !out || !peer_stage || !peer_res || !peer_flags) return PQ_ERR_NULL;
+  if (world < 2 || world > PQ_AR_MAX_WORLD || rank < 0 || rank >= world || n_elems <= 0) return PQ_ERR_SHAPE;
+  if ((n_elems * 2) % 16 || max_bytes % 256 || ((uintptr_t)in | (uintptr_t)out) & 15) return PQ_ERR_ALIGN;
+  if (n_elems * 2 > max_bytes || n_elems * 2 / 16 > INT32_MAX) return PQ_ERR_WORKSPACE;
+  return pq::allreduce_twostage_dispatch(in, out, n_elems, dtype, peer_stage, peer_res, peer_flags, rank, world,
+                                         max_bytes, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -9,7 +9,10 @@ reaches:
   CustomAllreduce                    device_communicators/custom_all_reduce.py:55-298
 Decode-sized messages go through the one-shot NVLink kernel in
 csrc/pq_allreduce.cu (each rank pushes its vector into every peer's buffer, one
-flag barrier, local fp32 sum in rank order); larger ones through NCCL.
+flag barrier, local fp32 sum in rank order) - or, at 1..8 tokens, ride in the
+row-parallel GEMV's own epilogue (csrc/pq_gemv_lut2.cu); messages up to 64 MiB
+(prefill) through the two-stage reduce-scatter + all-gather kernel over the same
+peer mappings, which is CUDA-graph capturable; anything larger through NCCL.
 """
 from __future__ import annotations
 
@@ -118,6 +121,9 @@ def tensor_model_parallel_all_reduce(input_: torch.Tensor) -> torch.Tensor:
         return input_
     if _ONESHOT is not None and _ONESHOT.eligible(input_):
         return _ONESHOT.all_reduce(input_)
+    if (_ONESHOT is not None and _ONESHOT.eligible_twostage(input_)
+            and os.environ.get("PQ_TWOSTAGE_ALLREDUCE", "1") != "0"):
+        return _ONESHOT.all_reduce_twostage(input_)      # above the one-shot limit: still one capturable kernel
     dist.all_reduce(input_, group=_TP_GROUP)     # input_ is a fresh GEMM output: in place is safe
     return input_
 
@@ -143,6 +149,9 @@ class OneShotAllReduce:
     # fused GEMV + all-reduce (csrc/pq_gemv_lut2.cu): receive buffer of {fp32, epoch} packets,
     # [2 parities][world][LL_SLOT_ELEMS]; 8 tokens (the table GEMV's limit) x 16384 outputs
     LL_SLOT_ELEMS = 8 * 16384
+    # two-stage all-reduce (csrc/pq_allreduce.cu) for messages above `max_bytes`: 2048 tokens x 8192
+    # hidden x 2 bytes = 32 MiB is Llama-2-70B's prefill partial sum; beyond 64 MiB NCCL takes over
+    TWOSTAGE_MAX_BYTES = 64 << 20
 
     def __init__(self, group: dist.ProcessGroup, max_bytes: int):
         from . import _lib
@@ -156,6 +165,8 @@ class OneShotAllReduce:
         # two staging slots (alternating by the device-side epoch parity) so that a fast
         # rank's next push cannot overwrite data a slow rank is still summing
         self.data = self.flags = self.ll_data = self.ll_state = None
+        self.stage2 = self.res2 = self.flags2 = None
+        self.res2_bytes = 2 * ((self.TWOSTAGE_MAX_BYTES // self.world + 255) // 256 * 256)
         mine = None
         try:
             self.data = self._malloc(2 * self.world * self.max_bytes)
@@ -163,12 +174,17 @@ class OneShotAllReduce:
             ll_bytes = 2 * self.world * self.LL_SLOT_ELEMS * 8
             self.ll_data = self._malloc(ll_bytes)
             self.ll_state = self._malloc(256)        # {epoch, ticket}: local only, never mapped by peers
+            self.stage2 = self._malloc(self.TWOSTAGE_MAX_BYTES)
+            self.res2 = self._malloc(self.res2_bytes)
+            self.flags2 = self._malloc(_lib.AR2_FLAG_BYTES)
             stream = torch.cuda.current_stream().cuda_stream
             _lib.check(self.lib.pq_b200_memset_async(self.flags, 0, _lib.AR_FLAG_BYTES, stream), "memset")
             _lib.check(self.lib.pq_b200_memset_async(self.ll_data, 0, ll_bytes, stream), "memset")
             _lib.check(self.lib.pq_b200_memset_async(self.ll_state, 0, 256, stream), "memset")
+            _lib.check(self.lib.pq_b200_memset_async(self.flags2, 0, _lib.AR2_FLAG_BYTES, stream), "memset")
             torch.cuda.synchronize()
-            mine = (self._handle(self.data), self._handle(self.flags), self._handle(self.ll_data))
+            mine = (self._handle(self.data), self._handle(self.flags), self._handle(self.ll_data),
+                    self._handle(self.stage2), self._handle(self.res2), self._handle(self.flags2))
         except Exception as exc:                       # noqa: BLE001 - the collective below must still run
             mine = None
             local_error = exc
@@ -181,13 +197,20 @@ class OneShotAllReduce:
         self.peer_data = (ctypes.c_void_p * self.world)()
         self.peer_flags = (ctypes.c_void_p * self.world)()
         self.peer_ll = (ctypes.c_void_p * self.world)()
-        for r, (hd, hf, hl) in enumerate(handles):
+        self.peer_stage2 = (ctypes.c_void_p * self.world)()
+        self.peer_res2 = (ctypes.c_void_p * self.world)()
+        self.peer_flags2 = (ctypes.c_void_p * self.world)()
+        for r, (hd, hf, hl, hs, hr, hf2) in enumerate(handles):
             if r == self.rank:
                 self.peer_data[r], self.peer_flags[r], self.peer_ll[r] = self.data, self.flags, self.ll_data
+                self.peer_stage2[r], self.peer_res2[r], self.peer_flags2[r] = self.stage2, self.res2, self.flags2
             else:
                 self.peer_data[r] = self._open(hd)
                 self.peer_flags[r] = self._open(hf)
                 self.peer_ll[r] = self._open(hl)
+                self.peer_stage2[r] = self._open(hs)
+                self.peer_res2[r] = self._open(hr)
+                self.peer_flags2[r] = self._open(hf2)
         # no barrier here: the caller (_setup_oneshot) ends with a group-wide agreement, which also
         # orders every rank's memset of its flags before any peer's first kernel
 
@@ -220,6 +243,20 @@ class OneShotAllReduce:
         return (t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous()
                 and nbytes % 16 == 0 and nbytes <= self.max_bytes and t.data_ptr() % 16 == 0)
 
+    def eligible_twostage(self, t: torch.Tensor) -> bool:
+        nbytes = t.numel() * t.element_size()
+        return (t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous()
+                and nbytes % 16 == 0 and nbytes <= self.TWOSTAGE_MAX_BYTES and t.data_ptr() % 16 == 0)
+
+    def all_reduce_twostage(self, t: torch.Tensor) -> torch.Tensor:
+        out = torch.empty_like(t)
+        dt = self._libmod.PQ_F16 if t.dtype == torch.float16 else self._libmod.PQ_BF16
+        rc = self.lib.pq_b200_allreduce_twostage(t.data_ptr(), out.data_ptr(), t.numel(), dt, self.peer_stage2,
+                                                 self.peer_res2, self.peer_flags2, self.rank, self.world,
+                                                 self.TWOSTAGE_MAX_BYTES, torch.cuda.current_stream().cuda_stream)
+        self._libmod.check(rc, "pq_b200_allreduce_twostage")
+        return out
+
     def all_reduce(self, t: torch.Tensor) -> torch.Tensor:
         out = torch.empty_like(t)
         dt = self._libmod.PQ_F16 if t.dtype == torch.float16 else self._libmod.PQ_BF16
@@ -235,7 +272,7 @@ class OneShotAllReduce:
             torch.cuda.synchronize()
             for p in self._opened:
                 self.lib.pq_b200_ipc_close_handle(p)
-            for p in (self.data, self.flags, self.ll_data, self.ll_state):
+            for p in (self.data, self.flags, self.ll_data, self.ll_state, self.stage2, self.res2, self.flags2):
                 if p:
                     self.lib.pq_b200_free(p)
         except Exception:
