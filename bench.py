@@ -428,8 +428,9 @@ def run_gpu_arm(args):
                 lins = [getattr(layer, name) for layer in model.layers]
                 k_in = lins[0].codes.shape[1] * d
                 xin = torch.randn(B, k_in, dtype=dtype, device=device)
-                g_k, _ = capture(lambda: [lin.quant_method.apply(lin, xin) for lin in lins], stream)
-                kernel_rows.append((name, lins[0], g_k, len(lins)))
+                g_k, outs = capture(lambda xin=xin, lins=lins: [lin.quant_method.apply(lin, xin) for lin in lins], stream)
+                # the graph holds raw pointers: its input and outputs must outlive it
+                kernel_rows.append((name, lins[0], g_k, len(lins), (xin, outs)))
 
     def run_step():
         if graph is not None:
@@ -465,7 +466,7 @@ def run_gpu_arm(args):
         ms_e2e = timed(step_e2e, args.steps)
         kernels = {}
         hbm_gbs, peak_src = measured_peaks()
-        for name, lin, g_k, n_l in kernel_rows:
+        for name, lin, g_k, n_l, _keep in kernel_rows:
             ms_k = timed(lambda: g_k.replay(), max(10, args.steps // 4)) / n_l
             ab = S.algorithmic_bytes(lin, B)
             kernels[name] = {"us": ms_k * 1e3, "algorithmic_bytes": ab, "gbs": ab / (ms_k * 1e-3) / 1e9}
