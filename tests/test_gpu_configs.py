@@ -150,3 +150,17 @@ def test_config4_70b_shard_shapes(tp, fmt):
             ct = dict(c)
             ct["x"] = c["x"][:t]
             check_sampled(gemm(g, parts, x=g["x"][:t]), ct, f"tp{tp}/{name}/t={t}")
+
+
+# ---- unaligned code pitch (Llama-2-7B down_proj shards at TP = 4 / 8: 344 / 172 code bytes per row) at
+# every token regime: the table GEMV's cp.async loader (1..8), the tcgen05 kernel's generic code path (9+)
+@pytest.mark.parametrize("k", [2752, 1376])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2)], ids=["8x8x1", "8x8x2"])
+def test_unaligned_pitch_all_token_counts(k, fmt):
+    b, d, m = fmt
+    c = O.make_case([4096], k, b, d, m, t=300, dtype=torch.float16, seed=17)
+    g = dev(c)
+    for t in (1, 2, 8, 9, 16, 64, 300):
+        ct = dict(c)
+        ct["x"] = c["x"][:t]
+        check_sampled(gemm(g, [4096], x=g["x"][:t]), ct, f"k={k} t={t}")

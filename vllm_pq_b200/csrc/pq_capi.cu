@@ -207,8 +207,8 @@ static int gemm_impl(const void* x, int64_t x_stride, const void* codes, const v
                      part_sizes, n_parts, dtype, algo, workspace, own, stream, 0);
   }
   if (was_auto && algo == PQ_ALGO_GEMV_LUT_TMA) {
-    // the one condition only the dispatcher can see: partition sizes that are not a multiple of
-    // the TMA super-row (odd row counts with an odd code pitch) - fall back to the other kernels
+    // conditions only the dispatcher can see (alignment of this call's pointers, the plan for these
+    // partition sizes): on PQ_ERR_UNSUPPORTED fall back to the other kernels
     rc = pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d,
                                 nbits, m, part_sizes, n_parts, dtype, workspace, workspace_bytes, s, xact, nullptr);
     if (rc != PQ_ERR_UNSUPPORTED) return rc;

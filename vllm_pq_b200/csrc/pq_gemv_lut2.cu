@@ -63,7 +63,6 @@ struct Lut2Args {
   long long x_stride, y_stride;
   int T, N, K, E, M;
   int Gp;                 // positions (= code bytes) per row
-  int R;                  // rows per TMA super-row (always 1: TMA rejects boxes that do not start on 16 bytes)
   const unsigned char* codes;
   int copy_w;             // 0: TMA.  4 / 8: the code pitch is not a multiple of 16 bytes (TP shards of
                           // down_proj) - the producer warp copies with cp.async of this width instead
@@ -1083,7 +1082,7 @@ int gemv_lut2_dispatch(const void* x, int64_t x_stride, const void* codes, const
   a.y = y; a.x_stride = x_stride; a.y_stride = y_stride;
   a.T = (int)t; a.N = (int)n; a.K = (int)k; a.E = 1 << nbits; a.M = m;
   a.m_log2 = m == 1 ? 0 : m == 2 ? 1 : 2;
-  a.Gp = (int)(k / d * m); a.R = 1; a.n_tiles = pl.n_tiles;
+  a.Gp = (int)(k / d * m); a.n_tiles = pl.n_tiles;
   a.codes = (const unsigned char*)codes;
   a.copy_w = a.Gp % 16 == 0 ? 0 : (a.Gp % 8 == 0 ? 8 : 4);
   a.S = pl.S; a.CS = pl.cs; a.cs_log2 = lut2_log2(pl.cs);
