@@ -147,3 +147,114 @@ def test_tp2_sharding_loaders_and_reduce(fmt):
                 pytest.fail("TP worker timed out")
             assert p.exitcode == 0, f"TP worker exit code {p.exitcode}"
         assert dict(ret) == {0: "ok", 1: "ok"}
+
+
+# ---- the fused-chain hooks and the vocabulary layers (N4) at world size 2 -------------
+# On the CPU the kernels do not exist, so the per-shard arithmetic is the ORACLE's, patched in for the
+# ops; what is under test is the host logic of the separate-launch form: all-reduce BEFORE the
+# residual add, bias on rank 0 only, sum of squares of the reduced stream, RMSNorm from that sum on
+# the next column-parallel layer, masked vocabulary-parallel lookup + all-reduce.
+def _worker_fused(rank: int, world: int, port: int, ret):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import vllm_pq_b200 as P
+        from oracle import pq_oracle as O
+        from vllm_pq_b200 import _custom_ops as ops
+        P.init_tensor_parallel()
+
+        def cpu_gemm(x, codes, codebooks, scales, parts, bias, algo=0):
+            return O.linear_fp32(x, codes, codebooks, scales, parts, bias).to(x.dtype)
+
+        def cpu_gemm_silu(x, codes, codebooks, scales, parts, bias, algo=0):
+            return cpu_gemm(O.silu_and_mul(x), codes, codebooks, scales, parts, bias)
+
+        def cpu_norm(x, residual, weight, eps):
+            out, z = O.fused_add_rms_norm(x, residual, weight, eps)
+            x.copy_(out)
+            if residual is not None:
+                residual.copy_(z)
+
+        def cpu_embedding(ids, codes, codebooks, scales):
+            w = O.dequantize_partitions(codes, codebooks, [codes.shape[0]], scales)
+            out = torch.zeros(ids.shape + (w.shape[1],), dtype=w.dtype)
+            ok = (ids >= 0) & (ids < w.shape[0])
+            out[ok] = w[ids[ok]]
+            return out
+        ops.pq_gemm, ops.pq_gemm_silu_mul, ops.fused_add_rms_norm, ops.pq_embedding = cpu_gemm, cpu_gemm_silu, cpu_norm, cpu_embedding
+
+        dt, eps = torch.float16, 1e-5
+        cfg = P.PQConfig(8, 8, 1, 1, lm_head_quantized=True)
+        hidden, inter, vocab = 256, 512, 300
+        kw = dict(bias=True, params_dtype=dt, quant_config=cfg)
+        o_full = O.make_case([hidden], hidden, 8, 8, 1, t=3, dtype=dt, seed=11, bias=True)
+        gate, up = (O.make_case([inter], hidden, 8, 8, 1, t=3, dtype=dt, seed=s) for s in (12, 13))
+        down_full = O.make_case([hidden], inter, 8, 8, 1, t=3, dtype=dt, seed=14)
+        for c in (o_full, gate, up, down_full):
+            c["codebooks"] = (c["codebooks"].float() / (c["codes"].shape[1] * 8) ** 0.5).to(dt)
+        o_l = P.RowParallelLinear(hidden, hidden, **kw)
+        gu_l = P.MergedColumnParallelLinear(hidden, [inter, inter], bias=False, params_dtype=dt, quant_config=cfg)
+        down_l = P.RowParallelLinear(inter, hidden, bias=False, params_dtype=dt, quant_config=cfg)
+        for name in ("codes", "codebooks", "scales"):
+            p = getattr(o_l, name); p.weight_loader(p, o_full[name])
+            p = getattr(down_l, name); p.weight_loader(p, down_full[name])
+            for sid, c in ((0, gate), (1, up)):
+                p = getattr(gu_l, name); p.weight_loader(p, c[name], sid)
+        o_l.bias.weight_loader(o_l.bias, o_full["bias"])
+
+        g = torch.Generator().manual_seed(3)
+        x = o_full["x"]
+        res = torch.randn(3, hidden, generator=g).to(dt)
+        w_norm = (torch.rand(hidden, generator=g) + 0.5).to(dt)
+        chunk = hidden // world
+        # o_proj: all-reduce, THEN the residual; bias enters once (linear.py:1206-1213, llama.py:276-283)
+        z, _, ssq = o_l(x[:, rank * chunk:(rank + 1) * chunk], residual=res, want_ssq=True)
+        z_ref = (O.linear_fp32(x, o_full["codes"], o_full["codebooks"], o_full["scales"], [hidden], o_full["bias"])
+                 .to(dt).float() + res.float())
+        torch.testing.assert_close(z.float(), z_ref, rtol=2e-2, atol=2e-2)
+        torch.testing.assert_close(ssq.sum(-1), z.float().pow(2).sum(-1), rtol=1e-4, atol=1e-4)
+        # gate_up with RMSNorm from the producer's sum of squares == RMSNorm launch + plain linear
+        y, _ = gu_l(z, input_norm=(ssq, w_norm, eps))
+        xn, _ = O.fused_add_rms_norm(z, None, w_norm, eps)
+        y_ref, _ = gu_l(xn)
+        torch.testing.assert_close(y.float(), y_ref.float(), rtol=2e-2, atol=2e-2)
+        # down_proj with SiLU*mul on its input, all-reduce, residual: against the full-tensor oracle
+        out, _ = down_l(y, input_act="silu_and_mul", residual=z)
+        acts = [torch.empty(3, inter // world, dtype=dt) for _ in range(world)]
+        dist.all_gather(acts, O.silu_and_mul(y).contiguous())
+        out_ref = O.linear_fp32(torch.cat(acts, -1), down_full["codes"], down_full["codebooks"], down_full["scales"],
+                                [hidden], None).float() + z.float()
+        torch.testing.assert_close(out.float(), out_ref, rtol=3e-2, atol=3e-2)
+        same = [torch.empty_like(out) for _ in range(world)]
+        dist.all_gather(same, out)
+        assert torch.equal(same[0], same[1])
+
+        # vocabulary-parallel embedding: 300 -> padded 320, 160 rows per rank; masked lookup + all-reduce
+        emb_full = O.make_case([vocab], hidden, 8, 8, 1, dtype=dt, seed=15)
+        emb = P.VocabParallelEmbedding(vocab, hidden, params_dtype=dt, quant_config=cfg)
+        assert emb.num_embeddings_per_partition == 160 and tuple(emb.codes.shape) == (160, hidden // 8, 1)
+        for name in ("codes", "codebooks", "scales"):
+            p = getattr(emb, name); p.weight_loader(p, emb_full[name])
+        ids = torch.tensor([[0, 159, 160, 299], [5, 200, 7, 161]])
+        got = emb(ids)
+        w_full = O.dequantize_partitions(emb_full["codes"], emb_full["codebooks"], [vocab], emb_full["scales"])
+        assert torch.equal(got, w_full[ids])
+        ret[rank] = "ok"
+    finally:
+        P.destroy_tensor_parallel()
+        dist.destroy_process_group()
+
+
+def test_tp2_fused_chain_hooks_and_vocab_layers():
+    world = 2
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker_fused, args=(r, world, port, ret)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(timeout=300)
+        assert dict(ret) == {0: "ok", 1: "ok"}, dict(ret)
