@@ -223,3 +223,41 @@ def test_lm_head_logits(t):
     logits = head.compute_logits(c["x"].cuda())
     assert logits.shape == (t, 32000)
     check_sampled(logits, c, "lm_head")
+
+
+# ---- nibble-packed private copy of 4-bit codes (repack in process_weights_after_loading) --
+@pytest.mark.parametrize("fmt", [(4, 8, 1), (4, 4, 1), (4, 8, 2), (4, 16, 2)], ids=["4x8x1", "4x4x1", "4x8x2", "4x16x2"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_nibble_packed_copy(fmt, dtype):
+    """Two 4-bit codes per byte + a 256-entry product codebook == the 4-bit layer: layer outputs against
+    the oracle (decode: packed copy; 16 tokens: checkpoint tensors), dequant untouched and bit-exact, the
+    M = 2 product codebook equal to the dequantised weights bit for bit."""
+    b, d, m = fmt
+    parts, k = [1024, 512], 2048
+    cfg = P.PQConfig(d, b, m, 1)
+    c = O.make_case(parts, k, b, d, m, t=16, dtype=dtype, seed=61)
+    c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).to(dtype)
+    with torch.device("cuda"):
+        lin = P.MergedColumnParallelLinear(k, parts, bias=False, params_dtype=dtype, quant_config=cfg)
+    lin.codes.data.copy_(c["codes"]); lin.codebooks.data.copy_(c["codebooks"]); lin.scales.data.copy_(c["scales"])
+    x = c["x"].cuda()
+    before = lin(x[:1])[0]
+    lin.quant_method.process_weights_after_loading(lin)
+    assert lin.codes_nibble.dtype == torch.int8 and lin.codebooks_pair.shape[1] == 256
+    g = k // d
+    assert tuple(lin.codes_nibble.shape) == ((sum(parts), g // 2, 1) if m == 1 else (sum(parts), g, 1))
+    assert lin.codebooks_pair.shape[3] == (2 * d if m == 1 else d)
+    for t in (1, 3, 8, 16):
+        y, _ = lin(x[:t])
+        ct = dict(c); ct["x"] = c["x"][:t]
+        ref = O.linear_fp32(ct["x"], c["codes"], c["codebooks"], c["scales"], parts, None)
+        err = O.error_report(y.cpu(), ref)
+        assert err["rms_rel"] < RMS_REL_TOL[dtype], (t, err)
+    rel = float((lin(x[:1])[0].double() - before.double()).pow(2).mean().sqrt() / before.double().pow(2).mean().sqrt())
+    assert rel < RMS_REL_TOL[dtype], rel
+    w = lin.quant_method.dequantize(lin, scaled=False)
+    w_ref = O.dequantize_partitions(c["codes"], c["codebooks"], parts, None)
+    assert torch.equal(w.cpu().view(torch.int16), w_ref.view(torch.int16))
+    # the packed copy dequantises to the same weights through the same kernel (an 8-bit PQ layer)
+    w_nib = P.ops.pq_dequant(lin.codes_nibble, lin.codebooks_pair, parts)
+    assert torch.equal(w_nib, w)

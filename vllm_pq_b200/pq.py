@@ -182,10 +182,60 @@ class PQLinearMethodBody:
             layer.codes_padded = padded
         elif hasattr(layer, "codes_padded"):
             del layer.codes_padded
+        self._repack_nibbles(layer)
+
+    @staticmethod
+    def _repack_nibbles(layer: torch.nn.Module) -> None:
+        """4-bit codes occupy a full int8 each in the checkpoint (aqlm.py:20-29: no sub-byte packing).
+        Two of them packed into one byte index a 256-entry PRODUCT codebook, which is again a PQ
+        layer the table GEMV already serves - half the bytes streamed, half the lookups:
+          * M = 1: the codes of two consecutive groups -> one group of 2d elements whose codeword is the
+            concatenation  cb'[lo | hi << 4] = (cb[lo] || cb[hi])            (d in {4, 8}, G even);
+          * M = 2: the two codes of one group -> one code whose codeword is the sum
+            cb'[lo | hi << 4] = cb0[lo] + cb1[hi], fp32 sum rounded once - exactly the dequantised
+            weight of aqlm.py:60-65, so the GEMV sees the weights ``pq::dequant`` returns.
+        Private copies (``codes_nibble`` [N, G', 1], ``codebooks_pair`` [P, 256, 1, d']), decode only
+        (1..8 tokens); the checkpoint tensors stay for every other kernel and for ``pq::dequant``."""
+        for name in ("codes_nibble", "codebooks_pair"):
+            if hasattr(layer, name):
+                delattr(layer, name)
+        codes, cb = layer.codes.data, layer.codebooks.data
+        n, g, m = codes.shape
+        pm, e, _, d = cb.shape
+        if e != 16 or not codes.is_cuda or codes.dtype != torch.int8:
+            return
+        idx = (codes.to(torch.int16) & 15)
+        p = pm // m
+        if m == 1 and d in (4, 8) and g % 2 == 0 and (g // 2) >= 64:
+            packed = (idx[:, 0::2, 0] | (idx[:, 1::2, 0] << 4))
+            lo = torch.arange(256, device=cb.device) & 15
+            hi = torch.arange(256, device=cb.device) >> 4
+            pair = torch.cat([cb[:, lo, 0, :], cb[:, hi, 0, :]], dim=-1)              # [P, 256, 2d]
+        elif m == 2 and d in (4, 8, 16) and g >= 64:
+            packed = (idx[:, :, 0] | (idx[:, :, 1] << 4))
+            lo = torch.arange(256, device=cb.device) & 15
+            hi = torch.arange(256, device=cb.device) >> 4
+            cbp = cb.view(p, 2, 16, d)
+            pair = (cbp[:, 0, lo, :].float() + cbp[:, 1, hi, :].float()).to(cb.dtype)   # [P, 256, d]
+        else:
+            return
+        packed = packed.to(torch.uint8).view(torch.int8).unsqueeze(-1).contiguous()     # signed storage, as codes
+        layer.codes_nibble = packed
+        layer.codebooks_pair = pair.unsqueeze(2).contiguous()
+
+    @staticmethod
+    def _decode_tensors(layer: torch.nn.Module):
+        """(codes, codebooks) the decode table GEMV streams: the nibble-packed private copy of a 4-bit
+        layer where there is one (process_weights_after_loading), else the checkpoint tensors."""
+        nib = getattr(layer, "codes_nibble", None)
+        if nib is not None:
+            return nib, layer.codebooks_pair
+        return layer.codes, layer.codebooks
 
     def _decode_fused_ok(self, layer: torch.nn.Module, x: torch.Tensor) -> bool:
-        n, g, m = layer.codes.shape
-        d, nbits = layer.codebooks.shape[3], layer.codebooks.shape[1].bit_length() - 1
+        codes, codebooks = self._decode_tensors(layer)
+        n, g, m = codes.shape
+        d, nbits = codebooks.shape[3], codebooks.shape[1].bit_length() - 1
         t = x.numel() // x.shape[-1] if x.shape[-1] else 0
         return x.is_cuda and t >= 1 and ops.gemm_fused_supported(t, n, g * d, d, nbits, m)
 
@@ -194,10 +244,12 @@ class PQLinearMethodBody:
         codebooks = layer.codebooks
         output_partition_sizes = getattr(codebooks, "output_partition_sizes", [])
         padded = getattr(layer, "codes_padded", None)
-        if padded is not None and self._decode_fused_ok(layer, x):
-            # decode over the padded private copy (process_weights_after_loading)
-            return ops.pq_gemm_fused(x, layer.codes, codebooks, layer.scales, list(output_partition_sizes),
-                                     bias, codes_padded=padded)[0]
+        nibble = getattr(layer, "codes_nibble", None)
+        if (padded is not None or nibble is not None) and self._decode_fused_ok(layer, x):
+            # decode over a private copy (process_weights_after_loading): padded rows / packed nibbles
+            dc, dcb = self._decode_tensors(layer)
+            return ops.pq_gemm_fused(x, dc, dcb, layer.scales, list(output_partition_sizes), bias,
+                                     codes_padded=padded if nibble is None else None)[0]
         # One op for every token count and format: the C side picks GEMV (decode) or the
         # tcgen05 GEMM (prefill). Reference dispatch for comparison: aqlm.py:344-374.
         return ops.pq_gemm(x, layer.codes, codebooks, layer.scales,
@@ -209,9 +261,11 @@ class PQLinearMethodBody:
         codebooks = layer.codebooks
         parts = list(getattr(codebooks, "output_partition_sizes", []))
         padded = getattr(layer, "codes_padded", None)
-        if padded is not None and self._decode_fused_ok(layer, x[..., : x.shape[-1] // 2]):
-            return ops.pq_gemm_fused(x, layer.codes, codebooks, layer.scales, parts, bias, silu_mul=True,
-                                     codes_padded=padded)[0]
+        nibble = getattr(layer, "codes_nibble", None)
+        if (padded is not None or nibble is not None) and self._decode_fused_ok(layer, x[..., : x.shape[-1] // 2]):
+            dc, dcb = self._decode_tensors(layer)
+            return ops.pq_gemm_fused(x, dc, dcb, layer.scales, parts, bias, silu_mul=True,
+                                     codes_padded=padded if nibble is None else None)[0]
         return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales, parts, bias)
 
     def apply_fused(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
@@ -226,8 +280,9 @@ class PQLinearMethodBody:
         from . import distributed as D
         codes, codebooks = layer.codes, layer.codebooks
         parts = list(getattr(codebooks, "output_partition_sizes", []))
-        n, g, m = codes.shape
-        d, nbits = codebooks.shape[3], codebooks.shape[1].bit_length() - 1
+        dc, dcb = self._decode_tensors(layer)        # what the table GEMV would stream (nibble-packed copy?)
+        n, g, m = dc.shape
+        d, nbits = dcb.shape[3], dcb.shape[1].bit_length() - 1
         t = x.numel() // x.shape[-1] if x.shape[-1] else 0
         comm = D.fused_allreduce_comm() if allreduce else None
         fused = (x.is_cuda and t >= 1 and ops.gemm_fused_supported(t, n, g * d, d, nbits, m)
@@ -238,10 +293,10 @@ class PQLinearMethodBody:
             norm = None
         if fused:
             ns, nw, ne = norm if norm is not None else (None, None, 1e-6)
-            y, ssq = ops.pq_gemm_fused(x, codes, codebooks, layer.scales, parts, bias, residual=residual,
+            y, ssq = ops.pq_gemm_fused(x, dc, dcb, layer.scales, parts, bias, residual=residual,
                                        norm_ssq=ns, norm_weight=nw, norm_eps=ne, allreduce=allreduce,
                                        silu_mul=silu_mul, want_ssq=want_ssq,
-                                       codes_padded=getattr(layer, "codes_padded", None))
+                                       codes_padded=getattr(layer, "codes_padded", None) if dc is codes else None)
             return y, (ssq if want_ssq else None)
         y = (ops.pq_gemm_silu_mul if silu_mul else ops.pq_gemm)(x, codes, codebooks, layer.scales, parts, bias)
         if allreduce:
