@@ -164,3 +164,24 @@ def test_unaligned_pitch_all_token_counts(k, fmt):
         ct = dict(c)
         ct["x"] = c["x"][:t]
         check_sampled(gemm(g, [4096], x=g["x"][:t]), ct, f"k={k} t={t}")
+
+
+@pytest.mark.parametrize("layer", MLP8B + [("qkv_parts", [1024, 128, 128], 4096)], ids=["gate_up8b", "down8b", "qkv_parts"])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_prefill_16bit_dense_weight_path(layer, dtype, monkeypatch):
+    """16-bit codes at >= 1024 tokens: the weight is dequantised once into the workspace and TMA-loaded as the
+    tcgen05 A operand.  Same operand bits, same accumulation order as the in-kernel dequant -> the SAME
+    output bits; and the ticket area at the head of the shared workspace stays zero (a K-group table
+    GEMV launched afterwards on the same stream still works)."""
+    _, parts, k = layer
+    c = O.make_case(parts, k, 16, 8, 1, t=1024, dtype=dtype, seed=19)
+    g = dev(c)
+    y = gemm(g, parts, _lib.ALGO_GEMM_TC)
+    check_sampled(y, c, "dense-A prefill")
+    # a table GEMV with K groups through the same workspace afterwards
+    c8 = O.make_case([4096], 11008, 8, 8, 1, t=1, dtype=dtype, seed=20)
+    g8 = dev(c8)
+    check_output(gemm(g8, [4096], _lib.ALGO_GEMV_LUT_TMA), c8, "table GEMV after the dense prefill")
+    # 1023 tokens take the in-kernel dequant: row 0..1022 must carry the same bits
+    y2 = gemm(g, parts, _lib.ALGO_GEMM_TC, x=g["x"][:1023])
+    assert torch.equal(y2, y[:1023])

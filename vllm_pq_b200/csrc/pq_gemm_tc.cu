@@ -59,6 +59,8 @@ struct TcArgs {
   float* ws_part;                          // ksplit > 1: [ksplit][T][N] fp32 partial sums (workspace)
   int* ws_tickets;                         // ksplit > 1: two counters per (token tile, row tile, epilogue warp); zero between launches
   unsigned long long* trace;               // PQ_TC_TRACE builds: 16 stamps per CTA
+  int dense_w;                             // 1: the A operand is TMA-loaded from a dense [N, K] weight (tmap_w) that
+                                           // pq_b200_dequant wrote into the workspace; the dequant warps idle
   int cb_smem_bytes;                       // 0: gather codewords from global memory (L2)
   int cb_stride;                           // bytes between codebook entries as staged (128 when replicated)
   int row_code_bytes;                      // bytes of codes per weight row
@@ -296,7 +298,8 @@ extern unsigned long long* g_lut_trace;
 // cp.async ring) or 0 (any M, codes read from global memory as needed).
 template <typename T, int D, typename CodeT, int MT>
 __global__ void __launch_bounds__(kTcThreads, 1)
-pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
+pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                  const TcArgs a) {
   extern __shared__ __align__(1024) unsigned char tc_smem[];
   __shared__ __align__(8) uint64_t bars[3 * kTcMaxStages + 4];
   __shared__ uint32_t tmem_base_s;
@@ -318,7 +321,9 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
   auto tmem_empty = [&](int i) { return bar0 + 8u * (3 * kTcMaxStages + 2 + i); };
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < a.stages; ++s) { mbar_init(full_a(s), 4); mbar_init(full_b(s), 1); mbar_init(empty(s), 1); }
+    for (int s = 0; s < a.stages; ++s) {
+      mbar_init(full_a(s), a.dense_w ? 1 : 4); mbar_init(full_b(s), 1); mbar_init(empty(s), 1);
+    }
     for (int i = 0; i < 2; ++i) { mbar_init(tmem_full(i), 1); mbar_init(tmem_empty(i), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" :: "l"(&tmap_x) : "memory");
@@ -344,10 +349,15 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
       int s = 0; uint32_t ph = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int tt = (tile / a.n_row_tiles) % a.n_tok_tiles, kb0 = (tile / tiles_per_split) * KB;
+        const int w_row0 = a.dense_w ? locate_row_block(a.parts, tile % a.n_row_tiles, kTcBM).row0 : 0;
         for (int kb = 0; kb < KB; ++kb) {
           mbar_wait(empty(s), ph ^ 1u);
           mbar_arrive_expect_tx(full_b(s), b_bytes);
           tma_load_2d(b_base + (uint32_t)s * b_bytes, &tmap_x, (kb0 + kb) * kTcBK, tt * a.BN, full_b(s));
+          if (a.dense_w) {                           // the weight tile too: [128 rows][64 k], same swizzle the dequant warps write
+            mbar_arrive_expect_tx(full_a(s), kTcABytes);
+            tma_load_2d(a_base + (uint32_t)s * kTcABytes, &tmap_w, (kb0 + kb) * kTcBK, w_row0, full_a(s));
+          }
           if (++s == a.stages) { s = 0; ph ^= 1u; }
         }
       }
@@ -383,7 +393,7 @@ pq_gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const TcArgs a) {
   } else if ((warp >= 4 && warp < 8) || warp >= 12) {
     // ===== dequant producers: one weight row per thread, group `grp` takes chunks grp, grp + G, ... =====
     const int grp = warp >= 12 ? 1 + ((warp - 12) >> 2) : 0;
-    const int G = a.groups;
+    const int G = a.dense_w ? 0 : a.groups;        // dense A operand: nothing to dequantise
     if (grp < G) {
     constexpr int GPB = kTcBK / D;
     constexpr int CBYTES = MT > 0 ? GPB * MT * (int)sizeof(CodeT) : 16;   // code bytes per row and k block
@@ -711,12 +721,41 @@ static int tc_ksplit(const TcPlan& pl, int64_t tiles, int64_t k) {
 }
 
 // Only decode-sized batches split K (a prefill has tiles to spare): tickets + kTcMaxSplit partial sums.
-int64_t gemm_tc_workspace(int64_t t, int64_t n, int64_t, int, int, int, int) {
+// 16-bit codes at prefill: the 65536-entry books live in L2 and every codeword is gathered once per weight
+// group AND token tile (8 times at 2048 tokens) - the kernel is L2-gather-bound at a third of its 8-bit
+// rate.  With a workspace for the dense weight, pq_b200_dequant writes W once (one gather per weight
+// group, the bits the in-kernel dequant would produce) and this kernel TMA-loads it as its A operand:
+// what the reference does with aqlm_dequant + cuBLAS (aqlm.py:132-156), minus the library GEMM.
+static bool tc_dense_prefill(int64_t t, int nbits) {
+  static const int off = [] { const char* e = getenv("PQ_TC_DENSE"); return e && atoi(e) == 0; }();
+  return !off && nbits > 8 && t >= 1024;
+}
+
+int64_t gemm_tc_workspace(int64_t t, int64_t n, int64_t k, int, int nbits, int, int) {
+  if (tc_dense_prefill(t, nbits)) return kTcTicketBytes + n * k * 2;    // W behind the ticket area, which stays zero
   return t <= 256 ? kTcTicketBytes + (int64_t)kTcMaxSplit * t * n * 4 : 0;
 }
 
+int dequant_dispatch(const void* codes, const void* codebooks, const void* scales, void* out, int64_t n, int64_t k,
+                     int d, int nbits, int m, const int64_t* part_sizes, int n_parts, int dtype, cudaStream_t stream);
+
+// dense [N, K] weight as a 2-D tensor map: box = 64 k x 128 rows, 128-byte swizzle (the A operand's layout)
+static int make_w_tmap(CUtensorMap* map, const void* w, int64_t n, int64_t k, int dtype) {
+  PFN_tmapEncodeTiled enc = tmap_encoder();
+  if (!enc) return PQ_ERR_UNSUPPORTED;
+  const cuuint64_t gdim[2] = {(cuuint64_t)k, (cuuint64_t)n};
+  const cuuint64_t gstride[1] = {(cuuint64_t)k * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)kTcBM};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, dtype == PQ_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                         const_cast<void*>(w), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? PQ_OK : PQ_ERR_ALIGN;
+}
+
 template <typename T, int D, typename CodeT, int MT>
-static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, cudaStream_t stream) {
+static int launch_tc(const CUtensorMap& map, const CUtensorMap& wmap, const TcArgs& a, const TcPlan& pl, cudaStream_t stream) {
   auto kern = pq_gemm_tc_kernel<T, D, CodeT, MT>;
   static bool attr_set[64] = {};
   int dev = 0;
@@ -728,18 +767,19 @@ static int launch_tc(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, 
   }
   const int tiles = a.n_tok_tiles * a.n_row_tiles * a.ksplit;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  kern<<<grid, kTcThreads, pl.smem_total, stream>>>(map, a);
+  kern<<<grid, kTcThreads, pl.smem_total, stream>>>(map, wmap, a);
   return (int)cudaGetLastError();
 }
 
 template <typename T, typename CodeT>
-static int launch_tc_d(const CUtensorMap& map, const TcArgs& a, const TcPlan& pl, int d, cudaStream_t stream) {
+static int launch_tc_d(const CUtensorMap& map, const CUtensorMap& wmap, const TcArgs& a, const TcPlan& pl, int d,
+                       cudaStream_t stream) {
 #define PQ_TC_MT(DD)                                                          \
   switch (pl.mt) {                                                            \
-    case 1: return launch_tc<T, DD, CodeT, 1>(map, a, pl, stream);            \
-    case 2: return launch_tc<T, DD, CodeT, 2>(map, a, pl, stream);            \
-    case 4: return launch_tc<T, DD, CodeT, 4>(map, a, pl, stream);            \
-    default: return launch_tc<T, DD, CodeT, 0>(map, a, pl, stream);           \
+    case 1: return launch_tc<T, DD, CodeT, 1>(map, wmap, a, pl, stream);            \
+    case 2: return launch_tc<T, DD, CodeT, 2>(map, wmap, a, pl, stream);            \
+    case 4: return launch_tc<T, DD, CodeT, 4>(map, wmap, a, pl, stream);            \
+    default: return launch_tc<T, DD, CodeT, 0>(map, wmap, a, pl, stream);           \
   }
   switch (d) {
     case 4: PQ_TC_MT(4)
@@ -777,14 +817,31 @@ int gemm_tc_dispatch(const void* x, int64_t x_stride, const void* codes, const v
       a.ws_part = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + kTcTicketBytes);
     }
   }
-  CUtensorMap map;
+  CUtensorMap map, wmap;
   rc = make_x_tmap(&map, x, x_stride, t, k, pl.bn, dtype);
   if (rc) return rc;
+  wmap = map;                                        // unused unless dense_w
+  if (tc_dense_prefill(t, nbits) && workspace && workspace_bytes >= kTcTicketBytes + n * k * 2 &&
+      ((uintptr_t)workspace & 127) == 0) {
+    void* w_dense = reinterpret_cast<unsigned char*>(workspace) + kTcTicketBytes;   // the first 64 KiB are tickets
+    rc = dequant_dispatch(codes, codebooks, nullptr, w_dense, n, k, d, nbits, m, part_sizes, n_parts, dtype, stream);
+    if (rc) return rc;
+    rc = make_w_tmap(&wmap, w_dense, n, k, dtype);
+    if (rc) return rc;
+    a.dense_w = 1;
+    // no codebooks and no code ring in shared memory: deeper pipeline
+    const int stage = kTcABytes + pl.bn * 128;
+    int stages = (225 * 1024 - 1024) / stage;
+    if (stages > kTcMaxStages) stages = kTcMaxStages;
+    if (stages > k / kTcBK) stages = (int)(k / kTcBK);
+    if (stages >= 2) { pl.stages = stages; pl.cb_smem = 0; pl.ring_bytes = 0; pl.smem_total = stages * stage + 1024; }
+    a.stages = pl.stages; a.cb_smem_bytes = pl.cb_smem;
+  }
   if (dtype == PQ_F16)
-    return nbits <= 8 ? launch_tc_d<__half, uint8_t>(map, a, pl, d, stream)
-                      : launch_tc_d<__half, uint16_t>(map, a, pl, d, stream);
-  return nbits <= 8 ? launch_tc_d<__nv_bfloat16, uint8_t>(map, a, pl, d, stream)
-                    : launch_tc_d<__nv_bfloat16, uint16_t>(map, a, pl, d, stream);
+    return nbits <= 8 ? launch_tc_d<__half, uint8_t>(map, wmap, a, pl, d, stream)
+                      : launch_tc_d<__half, uint16_t>(map, wmap, a, pl, d, stream);
+  return nbits <= 8 ? launch_tc_d<__nv_bfloat16, uint8_t>(map, wmap, a, pl, d, stream)
+                    : launch_tc_d<__nv_bfloat16, uint16_t>(map, wmap, a, pl, d, stream);
 }
 
 }  // namespace pq
