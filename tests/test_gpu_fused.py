@@ -261,3 +261,44 @@ def test_nibble_packed_copy(fmt, dtype):
     # the packed copy dequantises to the same weights through the same kernel (an 8-bit PQ layer)
     w_nib = P.ops.pq_dequant(lin.codes_nibble, lin.codebooks_pair, parts)
     assert torch.equal(w_nib, w)
+
+
+# ---- per-expert PQ linears: the quantised Mixtral MoE block --------------------------------
+@pytest.mark.parametrize("t", [1, 5, 40])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (16, 8, 1)], ids=["8x8x1", "16x8x1"])
+def test_mixtral_moe_block(t, fmt):
+    """mixtral_quant.py:98-160 over PQ experts: against the same formula evaluated with the oracle."""
+    import torch.nn.functional as F
+    b, d, m = fmt
+    dtype = torch.float16
+    hidden, ffn, n_exp, top_k = 1024, 2048, 4, 2
+    cfg = P.PQConfig(d, b, m, 1)
+    with torch.device("cuda"):
+        moe = P.PQMixtralMoE(n_exp, top_k, hidden, ffn, params_dtype=dtype, quant_config=cfg)
+    gen = torch.Generator().manual_seed(71)
+    cases = {}
+    for e in range(n_exp):
+        for name, n, k in (("w1", ffn, hidden), ("w3", ffn, hidden), ("w2", hidden, ffn)):
+            c = O.make_case([n], k, b, d, m, dtype=dtype, seed=100 + 10 * e + len(name) + ord(name[1]))
+            c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).to(dtype)
+            cases[(e, name)] = c
+            lin = getattr(moe.experts[e], name)
+            lin.codes.data.copy_(c["codes"]); lin.codebooks.data.copy_(c["codebooks"]); lin.scales.data.copy_(c["scales"])
+    gate = torch.randn(n_exp, hidden, generator=gen).to(dtype)
+    moe.gate_weight.data.copy_(gate)
+    x = torch.randn(t, hidden, generator=gen).to(dtype)
+    y = moe(x.cuda())
+    assert y.shape == (t, hidden)
+    # the same formula on the CPU: routing in the layer's dtype as there, experts in fp64
+    rw = F.softmax(F.linear(x.float(), gate.float()).to(dtype), dim=1, dtype=torch.float)
+    rw, sel = torch.topk(rw, top_k, dim=-1)
+    rw /= rw.sum(-1, keepdim=True)
+    ref = torch.zeros(t, hidden, dtype=torch.float64)
+    for e in range(n_exp):
+        wgt = (rw * (sel == e)).sum(-1, keepdim=True).double()
+        lin64 = lambda name, xin: O.linear_fp32(xin, cases[(e, name)]["codes"], cases[(e, name)]["codebooks"],   # noqa: E731
+                                                cases[(e, name)]["scales"], [cases[(e, name)]["codes"].shape[0]], None)
+        h = (F.silu(lin64("w1", x).to(dtype)) * lin64("w3", x).to(dtype))
+        ref += lin64("w2", h) * wgt
+    err = O.error_report(y.cpu(), ref)
+    assert err["rms_rel"] < 4e-3, err      # three roundings (w1/w3 outputs, the product, the weighted sum) above one linear's bound

@@ -42,3 +42,16 @@ def test_ops_have_no_cpu_path():
     emb = P.VocabParallelEmbedding(128, 64, params_dtype=torch.float16, quant_config=cfg)
     with pytest.raises(RuntimeError):
         emb(torch.zeros(3, dtype=torch.long))
+
+
+def test_mixtral_moe_block_parameters():
+    """Per-expert PQ linears (mixtral_quant.py:58-139): three ReplicatedLinear per expert carrying the PQ triple,
+    a dense router, all experts local at world size 1."""
+    cfg = P.PQConfig(8, 8, 2, 1)
+    moe = P.PQMixtralMoE(8, 2, 256, 512, params_dtype=torch.float16, quant_config=cfg)
+    assert moe.expert_indicies == list(range(8)) and all(e is not None for e in moe.experts)
+    e0 = moe.experts[0]
+    assert tuple(e0.w1.codes.shape) == (512, 32, 2) and tuple(e0.w2.codes.shape) == (256, 64, 2)
+    assert tuple(e0.w3.codebooks.shape) == (2, 256, 1, 8) and tuple(moe.gate_weight.shape) == (8, 256)
+    names = {n for n, _ in moe.named_parameters()}
+    assert "experts.3.w2.codes" in names and "experts.3.w2.scales" in names      # the checkpoint's tensor names

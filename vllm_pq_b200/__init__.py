@@ -20,6 +20,7 @@ from .distributed import (destroy_tensor_parallel, get_tensor_model_parallel_ran
 from .linear import (ColumnParallelLinear, LinearBase, MergedColumnParallelLinear,  # noqa: E402
                      QKVParallelLinear, ReplicatedLinear, RowParallelLinear)
 from .embedding import ParallelLMHead, VocabParallelEmbedding  # noqa: E402
+from .moe import PQMixtralMLP, PQMixtralMoE  # noqa: E402
 from .plugin_api import (LinearMethodBase, QuantizationConfig, get_quantization_config,  # noqa: E402
                          register_quantization_config)
 from .pq import PQConfig, PQLinearMethod, get_int_dtype  # noqa: E402
@@ -27,7 +28,7 @@ from .pq import PQConfig, PQLinearMethod, get_int_dtype  # noqa: E402
 __all__ = [
     "ops", "PQConfig", "PQLinearMethod", "get_int_dtype", "LinearBase", "ReplicatedLinear",
     "ColumnParallelLinear", "MergedColumnParallelLinear", "QKVParallelLinear", "RowParallelLinear",
-    "VocabParallelEmbedding", "ParallelLMHead", "QuantizationConfig", "LinearMethodBase", "register_quantization_config",
+    "VocabParallelEmbedding", "ParallelLMHead", "PQMixtralMLP", "PQMixtralMoE", "QuantizationConfig", "LinearMethodBase", "register_quantization_config",
     "get_quantization_config", "init_tensor_parallel", "destroy_tensor_parallel",
     "get_tensor_model_parallel_rank", "get_tensor_model_parallel_world_size",
     "tensor_model_parallel_all_reduce",
