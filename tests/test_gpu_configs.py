@@ -185,3 +185,30 @@ def test_prefill_16bit_dense_weight_path(layer, dtype, monkeypatch):
     # 1023 tokens take the in-kernel dequant: row 0..1022 must carry the same bits
     y2 = gemm(g, parts, _lib.ALGO_GEMM_TC, x=g["x"][:1023])
     assert torch.equal(y2, y[:1023])
+
+
+# ---- Llama-2-7B TP = 2 / 4 / 8 shard shapes through the table GEMV (what the SCALE run launches) -------------
+def shards_7b(tp):
+    return [("qkv", [4096 // tp] * 3, 4096), ("o", [4096], 4096 // tp),
+            ("gate_up", [11008 // tp] * 2, 4096), ("down", [4096], 11008 // tp)]
+
+
+@pytest.mark.parametrize("tp", [2, 4, 8])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2)], ids=["8x8x1", "8x8x2"])
+def test_7b_tp_shard_shapes_table_gemv(tp, fmt):
+    """Every plan the planner picks for the TP shards (16-CTA clusters of the 8-warp shape with two row
+    iterations for down_proj at TP = 2, clusters wider than the tile count at TP = 4 / 8, the cp.async
+    loader for unaligned pitches): against the oracle, reproducible bit for bit, 1 / 2 / 8 tokens."""
+    b, d, m = fmt
+    lib = _lib.load()
+    for name, parts, k in shards_7b(tp):
+        c = O.make_case(parts, k, b, d, m, t=8, dtype=torch.float16, seed=23 + tp)
+        g = dev(c)
+        for t in (1, 2, 8):
+            if not lib.pq_b200_algo_supported(_lib.ALGO_GEMV_LUT_TMA, t, sum(parts), k, d, b, m):
+                continue
+            ct = dict(c)
+            ct["x"] = c["x"][:t]
+            y = gemm(g, parts, _lib.ALGO_GEMV_LUT_TMA, x=g["x"][:t])
+            check_output(y, ct, f"tp{tp}/{name}/t={t}")
+            assert torch.equal(y, gemm(g, parts, _lib.ALGO_GEMV_LUT_TMA, x=g["x"][:t])), (tp, name, t)

@@ -38,6 +38,7 @@ SHAPES = {
     "down70b": ([8192], 28672),
     "down7b_tp4": ([4096], 2752),      # row-parallel shards: code pitch 344 / 172 bytes (not a multiple of 16)
     "down7b_tp8": ([4096], 1376),
+    "down7b_tp2": ([4096], 5504),
     "n4096k1024": ([4096], 1024), "n4096k256": ([4096], 256), "n512k4096": ([512], 4096), "n128k256": ([128], 256),
 }
 

@@ -880,7 +880,10 @@ static bool lut2_plan(Lut2Plan& pl, int64_t t, int64_t n, int64_t k, int d, int 
         // measured on B200 (gpurun r2_01, profiles/r2_01_*): the 8-warp CTA wins only where a CTA has a
         // single item (o_proj: 4.6 against 5.0 us); with more items its half-size lookup crew loses
         // more than the co-resident prologue gains (qkv 6.7 / 6.3, gate_up 8.7 / 7.6, down 9.2 / 8.1 us)
-        if (cw == 8 && !force_cw && S * n_iter > 1) continue;
+        // ... except with a 16-CTA cluster (8-warp shape only) that gives every CTA ONE tile: saving the
+        // second table build outweighs a second row iteration (down_proj shard at TP = 2, 11 tiles:
+        // 5.08 us against 5.91 us for 8 CTAs x 2 tiles of the 16-warp shape; gpurun r2_37)
+        if (cw == 8 && !force_cw && S * n_iter > 1 && !(cs == 16 && S == 1 && n_iter <= 2)) continue;
         int stages = force_stages ? min(kL2MaxStages, max(1, force_stages)) : min(cw == 8 ? kL2MaxStages : 4, max(2, S * n_iter));
         auto smem_of = [&](int st) { return lut2_smem_bytes(E, st, cw, pl.smem_cb, smem_x, rows); };
         while (stages > (cw == 8 ? 1 : 2) && smem_of(stages) > smem_cap) --stages;
