@@ -182,3 +182,41 @@ def test_silu_mul_ops_fake_shapes_and_hook_checks():
     from oracle import pq_oracle as O
     v = torch.tensor([[1.0, -2.0, 0.5, 3.0]], dtype=torch.float16)
     assert torch.equal(O.silu_and_mul(v), torch.nn.functional.silu(v[:, :2]) * v[:, 2:])
+
+
+def test_round2_entry_points_reject_bad_arguments_without_gpu():
+    """The new C entry points validate before any CUDA call (include/pq_b200.h): fused GEMV, norm,
+    embedding, two-stage all-reduce; and the fused-support predicate follows its contract."""
+    lib = _lib.load()
+    parts, n_parts = _lib.parts_array([4096])
+    sup = lib.pq_b200_gemm_fused_supported
+    assert sup(1, 4096, 4096, 8, 8, 1) == 1 and sup(8, 4096, 4096, 8, 8, 2) == 1
+    assert sup(9, 4096, 4096, 8, 8, 1) == 0            # more than 8 tokens: separate launches
+    assert sup(1, 4096, 4096, 8, 4, 1) == 0            # 4-bit codes as stored (the nibble-packed copy is 8-bit)
+    assert sup(1, 4096, 4096, 8, 16, 1) == 0           # 16-bit codes: no table GEMV
+    assert sup(1, 4096, 4095, 8, 8, 1) == 0
+    assert lib.pq_b200_gemm_fused_slots(1, 4096, 4096, 8, 8, 1, parts, n_parts, 0) > 0
+    assert lib.pq_b200_gemm_fused_slots(1, 4096, 4096, 8, 16, 1, parts, n_parts, 0) == -7
+    ep = _lib.Epilogue()
+    gf = lib.pq_b200_gemm_fused
+    args = lambda **kw: [kw.get("x", 16), 4096, 16, 16, 16, None, 16, 4096, kw.get("t", 1), 4096, 4096, 8,   # noqa: E731
+                         kw.get("nbits", 8), 1, parts, n_parts, kw.get("dtype", 0), None, 0, None, ctypes.byref(ep)]
+    assert gf(*args(dtype=5)) == -1
+    assert gf(*args(x=None)) == -6
+    assert gf(*args(nbits=16)) == -7
+    assert gf(*args(t=9)) == -7
+    norm = lib.pq_b200_fused_add_rms_norm
+    assert norm(16, 64, None, 0, 16, 1e-5, 1, 64, 3, None) == -1
+    assert norm(None, 64, None, 0, 16, 1e-5, 1, 64, 0, None) == -6
+    assert norm(16, 32, None, 0, 16, 1e-5, 1, 64, 0, None) == -3          # row stride shorter than the row
+    emb = lib.pq_b200_embedding
+    assert emb(None, 1, 16, 16, 16, 16, 64, 16, 64, 8, 8, 1, 0, None) == -6
+    assert emb(16, 1, 16, 16, 16, 16, 32, 16, 64, 8, 8, 1, 0, None) == -3  # out stride shorter than k
+    assert emb(16, 1, 16, 16, 16, 16, 64, 16, 64, 5, 8, 1, 0, None) in (-2, -3)   # d = 5
+    assert emb(16, 0, 16, 16, 16, 16, 64, 16, 64, 8, 8, 1, 0, None) == 0   # no ids: nothing is launched
+    two = lib.pq_b200_allreduce_twostage
+    ptrs = (ctypes.c_void_p * 2)(16, 16)
+    assert two(16, 16, 64, 7, ptrs, ptrs, ptrs, 0, 2, 1 << 20, None) == -1
+    assert two(16, 16, 64, 0, ptrs, ptrs, ptrs, 2, 2, 1 << 20, None) == -3            # rank out of range
+    assert two(16, 16, 60, 0, ptrs, ptrs, ptrs, 0, 2, 1 << 20, None) == -4            # not a multiple of 16 bytes
+    assert two(16, 16, 1 << 20, 0, ptrs, ptrs, ptrs, 0, 2, 1 << 20, None) == -5       # larger than the buffers
