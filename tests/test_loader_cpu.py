@@ -101,3 +101,101 @@ def test_quant_config_gate():
         L.quant_config_from_hf({"model_type": "llama"})
     with pytest.raises(ValueError):
         L.quant_config_from_hf({"quantization_config": {"quant_method": "gptq"}})
+
+
+# ---- vocabulary layers and Mixtral experts -----------------------------------------
+class TinyMoEModel(torch.nn.Module):
+    """embed_tokens + lm_head + two layers of {attention projections, MoE block}: the module names an HF
+    Mixtral checkpoint uses (mixtral_quant.py:300-330 in the reference)."""
+
+    def __init__(self, cfg, vocab=100, hidden=128, ffn=256, experts=4, tie=False):
+        super().__init__()
+        from vllm_pq_b200.embedding import ParallelLMHead, VocabParallelEmbedding
+        from vllm_pq_b200.moe import PQMixtralMoE
+        kw = dict(params_dtype=torch.float16, quant_config=cfg)
+        self.embed_tokens = VocabParallelEmbedding(vocab, hidden, prefix="model.embed_tokens", **kw)
+        self.lm_head = ParallelLMHead(vocab, hidden, prefix="lm_head", **kw)
+        if tie:
+            self.lm_head.tie_weights(self.embed_tokens)
+        self.layers = torch.nn.ModuleList()
+        for _ in range(2):
+            layer = torch.nn.Module()
+            layer.block_sparse_moe = PQMixtralMoE(experts, 2, hidden, ffn, **kw)
+            self.layers.append(layer)
+
+
+def moe_checkpoint(fmt, vocab=100, hidden=128, ffn=256, experts=4, lm_head=True):
+    b, d, m = fmt
+    tensors, full, seed = {}, {}, 100
+
+    def put(prefix, n, k):
+        nonlocal seed
+        seed += 1
+        c = O.make_case([n], k, b, d, m, t=1, dtype=torch.float16, seed=seed)
+        full[prefix] = c
+        for key in ("codes", "codebooks", "scales"):
+            tensors[f"{prefix}.{key}"] = c[key].contiguous()
+
+    put("model.embed_tokens", vocab, hidden)
+    if lm_head:
+        put("lm_head", vocab, hidden)
+    for layer in range(2):
+        for e in range(experts):
+            put(f"model.layers.{layer}.block_sparse_moe.experts.{e}.w1", ffn, hidden)
+            put(f"model.layers.{layer}.block_sparse_moe.experts.{e}.w2", hidden, ffn)
+            put(f"model.layers.{layer}.block_sparse_moe.experts.{e}.w3", ffn, hidden)
+        tensors[f"model.layers.{layer}.block_sparse_moe.gate.weight"] = torch.randn(experts, hidden).half()
+        tensors[f"model.layers.{layer}.input_layernorm.weight"] = torch.ones(hidden, dtype=torch.float16)
+    return tensors, full
+
+
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (16, 8, 1)])
+def test_vocab_layers_and_experts_are_placed(fmt):
+    b, d, m = fmt
+    cfg = P.PQConfig(d, b, m, 1, lm_head_quantized=True)
+    model = TinyMoEModel(cfg)
+    tensors, full = moe_checkpoint(fmt)
+    loaded, skipped = L.load_pq_linears(model, tensors.items())
+    assert skipped == [n for n in tensors if "input_layernorm" in n]
+    want = {n for n, _ in model.named_parameters()}
+    assert loaded == want, sorted(want - loaded)
+    # vocabulary: 100 rows of the checkpoint, 28 zero rows of padding (a zero scale -> a zero row)
+    for mod, prefix in ((model.embed_tokens, "model.embed_tokens"), (model.lm_head, "lm_head")):
+        c = full[prefix]
+        assert mod.codes.shape[0] == 128
+        assert torch.equal(mod.codes[:100], c["codes"]) and torch.equal(mod.scales[:100], c["scales"])
+        assert torch.equal(mod.codebooks, c["codebooks"])
+        assert not mod.codes[100:].any() and not mod.scales[100:].any()
+    for li, layer in enumerate(model.layers):
+        moe = layer.block_sparse_moe
+        assert torch.equal(moe.gate_weight, tensors[f"model.layers.{li}.block_sparse_moe.gate.weight"])
+        for e, expert in enumerate(moe.experts):
+            for w in ("w1", "w2", "w3"):
+                c = full[f"model.layers.{li}.block_sparse_moe.experts.{e}.{w}"]
+                for key in ("codes", "codebooks", "scales"):
+                    assert torch.equal(getattr(getattr(expert, w), key), c[key])
+
+
+def test_tied_lm_head_and_mismatches():
+    cfg = P.PQConfig(8, 8, 1, 1, lm_head_quantized=True)
+    tied = TinyMoEModel(cfg, tie=True)
+    assert "lm_head.codes" not in dict(tied.named_parameters())
+    tensors, full = moe_checkpoint((8, 8, 1))
+    loaded, skipped = L.load_pq_linears(tied, tensors.items())       # lm_head.* in the file: consumed, not placed
+    assert not any("lm_head" in n for n in loaded) and not any("lm_head" in s for s in skipped)
+    assert torch.equal(tied.lm_head.codes[:100], full["model.embed_tokens"]["codes"])
+    # an expert index the model does not have, and a MoE tensor for a layer without a MoE block
+    model = TinyMoEModel(cfg, experts=2)
+    with pytest.raises(KeyError, match="experts.2"):
+        L.load_pq_linears(model, tensors.items())
+    model = TinyMoEModel(cfg)
+    extra = {"model.layers.5.block_sparse_moe.experts.0.w1.codes": tensors["model.layers.0.block_sparse_moe.experts.0.w1.codes"]}
+    with pytest.raises(KeyError, match="no MoE block"):
+        L.load_pq_linears(model, extra.items())
+    bad = {"model.layers.0.block_sparse_moe.gate.weight": torch.zeros(3, 128).half()}
+    with pytest.raises(ValueError, match="shape"):
+        L.load_pq_linears(model, bad.items())
+    # a dense model (the Llama stack) still reports PQ vocabulary tensors as skipped
+    stack = S.PQLlamaLinearStack(SHAPE, P.PQConfig(8, 8, 1, 1), torch.float16)
+    _, skipped = L.load_pq_linears(stack, {"model.embed_tokens.codes": tensors["model.embed_tokens.codes"]}.items())
+    assert skipped == ["model.embed_tokens.codes"]

@@ -240,6 +240,26 @@ def _worker_fused(rank: int, world: int, port: int, ret):
         got = emb(ids)
         w_full = O.dequantize_partitions(emb_full["codes"], emb_full["codebooks"], [vocab], emb_full["scales"])
         assert torch.equal(got, w_full[ids])
+
+        # checkpoint walk at world size 2: this rank's vocabulary rows and experts are placed, the other
+        # rank's experts are consumed without being reported (mixtral_quant.py:436-439)
+        from tests.test_loader_cpu import TinyMoEModel, moe_checkpoint
+        from vllm_pq_b200 import loader as L
+        model = TinyMoEModel(P.PQConfig(8, 8, 1, 1, lm_head_quantized=True))
+        tensors, full = moe_checkpoint((8, 8, 1))
+        loaded, skipped = L.load_pq_linears(model, tensors.items())
+        assert loaded == {n for n, _ in model.named_parameters()}
+        assert skipped == [n for n in tensors if "input_layernorm" in n]
+        mine = [2 * rank, 2 * rank + 1]
+        moe = model.layers[1].block_sparse_moe
+        assert moe.expert_indicies == mine and all((moe.experts[e] is not None) == (e in mine) for e in range(4))
+        for e in mine:
+            c = full[f"model.layers.1.block_sparse_moe.experts.{e}.w2"]
+            assert torch.equal(moe.experts[e].w2.codes, c["codes"]) and torch.equal(moe.experts[e].w2.scales, c["scales"])
+        c = full["lm_head"]                                   # 100 rows -> padded 128, 64 per rank
+        have = 64 if rank == 0 else 36
+        assert torch.equal(model.lm_head.codes[:have], c["codes"][64 * rank:64 * rank + have])
+        assert not model.lm_head.scales[have:].any()
         ret[rank] = "ok"
     finally:
         P.destroy_tensor_parallel()

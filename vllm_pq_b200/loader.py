@@ -13,9 +13,20 @@ Mirrors the part of the reference's model loading that touches the PQ path:
 
 An AQLM checkpoint stores, per linear, `<prefix>.codes [N, G, M]`, `<prefix>.codebooks
 [M, 2^b, 1, d]` and `<prefix>.scales [N, 1, 1, 1]` - exactly the tensors `create_weights` registers,
-so the weight loaders only narrow (tensor parallelism) and place (fused layers); nothing is
-repacked.  Tensors that are not part of the PQ linears (embeddings, norms, lm_head, rotary caches)
-are outside this package's scope: they are returned as `skipped`, not loaded.
+so the weight loaders only narrow (tensor parallelism) and place (fused layers): the PARAMETERS
+keep the checkpoint's layout.  `load_checkpoint` then runs `process_weights_after_loading`, which
+may add private device copies next to them (codes rows padded to a 16-byte pitch for TMA, 4-bit codes
+packed two to a byte against a product codebook - DESIGN.md 4); those are derived data, never loaded.
+
+Beyond the four Llama projections the walk also places
+* the vocabulary layers when the model holds PQ ones (`embed_tokens`, `lm_head` of
+  vllm_pq_b200/embedding.py - a checkpoint whose config says `lm_head_quantized`): the rank's rows of
+  `model.embed_tokens.{codes,codebooks,scales}` / `lm_head.*` (vocab_parallel_embedding.py:361-393);
+* the experts of a quantised Mixtral block (`layers.N.block_sparse_moe.experts.E.w1|w2|w3.*` and the
+  dense router `...gate.weight`), skipping experts that live on another rank
+  (mixtral_quant.py:436-439).
+Everything else (dense embeddings, norms, rotary caches) is outside this package's scope and is
+returned as `skipped`, not loaded.
 """
 from __future__ import annotations
 
@@ -39,6 +50,9 @@ STACKED_PARAMS_MAPPING = [
 ]
 
 _LAYER_RE = re.compile(r"^(?:model\.)?layers\.(\d+)\.(?:self_attn|mlp)(\..+)$")
+_VOCAB_RE = re.compile(r"^(?:model\.)?(embed_tokens|lm_head)\.(codes|codebooks|scales|bias)$")
+_MOE_RE = re.compile(r"^(?:model\.)?layers\.(\d+)\.block_sparse_moe\.(experts\.(\d+)\.w[123]\.\w+|gate\.weight)$")
+_PQ_KEYS = ("codes", "codebooks", "scales")
 
 
 def quant_config_from_hf(config: Dict) -> PQConfig:
@@ -78,9 +92,65 @@ def _target_name(name: str):
     return int(m.group(1)), m.group(2)
 
 
+def _load_vocab(name: str, tensor: torch.Tensor, stack: torch.nn.Module, params_dict, loaded: Set[str]) -> bool:
+    """`model.embed_tokens.codes` / `lm_head.scales` ... -> the PQ vocabulary layer of that name, if the
+    model has one.  A PQ tensor for a vocabulary layer the model keeps dense (or lacks) is an error
+    only when the OTHER vocabulary layer is a PQ one - then the checkpoint and the model disagree."""
+    m = _VOCAB_RE.match(name)
+    if not m:
+        return False
+    pname = f"{m.group(1)}.{m.group(2)}"
+    if pname not in params_dict:
+        if m.group(2) == "bias":
+            return False
+        if getattr(getattr(stack, m.group(1), None), m.group(2), None) is not None:
+            return True                                 # tied to the other layer's parameter: already placed
+        if any(p.split(".")[0] in ("embed_tokens", "lm_head") for p in params_dict):
+            raise KeyError(f"{name}: the model has no parameter {pname}")
+        return False
+    param = params_dict[pname]
+    param.weight_loader(param, tensor)
+    loaded.add(pname)
+    return True
+
+
+def _load_moe(name: str, tensor: torch.Tensor, stack: torch.nn.Module, params_dict, loaded: Set[str]) -> bool:
+    """Mixtral expert / router tensors (mixtral_quant.py:432-446).  Returns True when the name was
+    consumed: loaded, or an expert of another rank (skipped on purpose, not reported as `skipped`)."""
+    m = _MOE_RE.match(name)
+    if not m:
+        return False
+    layer, tail = int(m.group(1)), m.group(2)
+    base = f"layers.{layer}.block_sparse_moe"
+    if not any(p.startswith(base + ".") for p in params_dict):
+        if any(".block_sparse_moe." in p for p in params_dict):
+            raise KeyError(f"{name}: the model has no MoE block in layer {layer}")
+        return False
+    pname = f"{base}.gate_weight" if tail == "gate.weight" else f"{base}.{tail}"
+    if pname not in params_dict:
+        if tail == "gate.weight" or pname.endswith(".bias"):
+            return False
+        moe = stack.get_submodule(base)
+        expert = int(m.group(3))
+        if expert >= len(moe.experts) or tail.rsplit(".", 1)[-1] not in _PQ_KEYS:
+            raise KeyError(f"{name}: the model has no parameter {pname}")
+        return True                                     # another rank's expert
+    param = params_dict[pname]
+    loader = getattr(param, "weight_loader", None)
+    if loader is None:                                  # the dense router: a plain parameter
+        if param.shape != tensor.shape:
+            raise ValueError(f"{name}: shape {tuple(tensor.shape)} != {tuple(param.shape)}")
+        param.data.copy_(tensor)
+    else:
+        loader(param, tensor)
+    loaded.add(pname)
+    return True
+
+
 def load_pq_linears(stack: torch.nn.Module, weights: Iterable[Tuple[str, torch.Tensor]]):
     """Route checkpoint tensors into the PQ linears of `stack` (a PQLlamaLinearStack, or any module
-    with `.layers[i].{qkv_proj,o_proj,gate_up_proj,down_proj}`).
+    with `.layers[i].{qkv_proj,o_proj,gate_up_proj,down_proj}`; optionally `.embed_tokens`, `.lm_head`
+    and `.layers[i].block_sparse_moe`).
 
     Returns (loaded, skipped): the parameter names that received data, and the checkpoint names
     that do not belong to a PQ linear.  Raises KeyError for a tensor that names a PQ linear the
@@ -92,7 +162,9 @@ def load_pq_linears(stack: torch.nn.Module, weights: Iterable[Tuple[str, torch.T
     for name, tensor in weights:
         tgt = _target_name(name)
         if tgt is None or "rotary_emb" in name:
-            skipped.append(name)
+            if not (_load_vocab(name, tensor, stack, params_dict, loaded)
+                    or _load_moe(name, tensor, stack, params_dict, loaded)):
+                skipped.append(name)
             continue
         layer, suffix = tgt
         for param_name, weight_name, shard_id in STACKED_PARAMS_MAPPING:
@@ -126,7 +198,7 @@ def load_checkpoint(stack: torch.nn.Module, checkpoint_dir: str, strict: bool = 
     the stack must have been covered by the checkpoint."""
     loaded, skipped = load_pq_linears(stack, safetensors_weights_iterator(checkpoint_dir))
     if strict:
-        want = {n for n, _ in stack.named_parameters() if n.rsplit(".", 1)[-1] in ("codes", "codebooks", "scales")}
+        want = {n for n, _ in stack.named_parameters() if n.rsplit(".", 1)[-1] in _PQ_KEYS}
         missing = sorted(want - loaded)
         if missing:
             raise KeyError(f"checkpoint does not cover {len(missing)} PQ parameters, e.g. {missing[:4]}")
