@@ -193,7 +193,8 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
     """SiluAndMul.forward_native (vllm/model_executor/layers/activation.py:73-76): the CPU path of
     the MLP's act_fn (llama.py:89-93).  The CUDA kernel (csrc/activation_kernels.cu:35-38) rounds
     the same way - SiLU in fp32 rounded to the dtype, then the product rounded to the dtype - so the
-    two agree to the last bit except where expf differs by an ulp across a rounding boundary."""
+    two agree to the last bit except where expf differs by an ulp across a rounding boundary.
+    Pinned bit for bit to the reference's method (tests/golden/layers/silu_*.npz)."""
     d = x.shape[-1] // 2
     return F.silu(x[..., :d]) * x[..., d:]
 
@@ -205,7 +206,10 @@ def fused_add_rms_norm(x: torch.Tensor, residual: Optional[torch.Tensor], weight
     llama.py:272-283):  z = x + residual rounded to the dtype (:75-80, packed half add);
     variance = mean of float(z)^2 (:79,:82-88); out = T(T(float(z) * rstd) * weight) (:91-97: two
     roundings).  The sum of squares is taken in fp64 here - the kernel's fp32 block reduction has no
-    fixed order, so rstd may differ from it in the last fp32 bit."""
+    fixed order, so rstd may differ from it in the last fp32 bit.
+    Pinned (tests/test_oracle_golden.py, tests/golden/layers/norm_*.npz): the new residual is bit-equal
+    to RMSNorm.forward_native's (layers/layernorm.py:45-48) and the output is within the two ulps that
+    last bit allows of forward_native applied to that rounded residual."""
     z = x if residual is None else (x.float() + residual.float()).to(x.dtype)
     var = z.double().pow(2).mean(-1, keepdim=True)
     rstd = torch.rsqrt(var + eps).float()

@@ -82,3 +82,60 @@ def load_reference_aqlm():
         sys.modules.update(saved)
     _cached = mod
     return mod
+
+
+_cached_layers = None
+
+
+def load_reference_layers():
+    """(RMSNorm, SiluAndMul): the reference's own layer classes out of layers/layernorm.py and
+    layers/activation.py, executed unmodified under stubs, for their ``forward_native`` - the
+    reference's CPU form of the ops the fused epilogue replaces.  The stubs:
+    ``CustomOp`` is an nn.Module whose ``register`` decorator does nothing; ``current_platform``
+    answers False to every ``is_*`` question (no native op is looked up); the TP helpers say 1 rank."""
+    global _cached_layers
+    if _cached_layers is not None:
+        return _cached_layers
+    if not available():
+        raise FileNotFoundError(f"reference not present under {REF_ROOT}")
+    saved = {k: v for k, v in sys.modules.items() if k == "vllm" or k.startswith("vllm.")}
+    try:
+        for name in ("vllm", "vllm.distributed", "vllm.model_executor", "vllm.model_executor.custom_op",
+                     "vllm.model_executor.utils", "vllm.platforms", "vllm.utils", "vllm.model_executor.layers"):
+            sys.modules[name] = types.ModuleType(name)
+
+        class CustomOp(torch.nn.Module):              # model_executor/custom_op.py: dispatch only
+            @classmethod
+            def register(cls, name):
+                return lambda op_cls: op_cls
+
+            def forward(self, *args, **kwargs):
+                return self.forward_native(*args, **kwargs)
+
+        class _Platform:
+            def __getattr__(self, name):
+                if name.startswith("is_"):
+                    return lambda *a, **k: False
+                raise AttributeError(name)
+
+        class LazyDict(dict):                          # vllm/utils.py: values are factories
+            def __getitem__(self, key):
+                return super().__getitem__(key)()
+
+        sys.modules["vllm.model_executor.custom_op"].CustomOp = CustomOp
+        dist = sys.modules["vllm.distributed"]
+        dist.divide = lambda a, b: a // b
+        dist.get_tensor_model_parallel_rank = lambda: 0
+        dist.get_tensor_model_parallel_world_size = lambda: 1
+        sys.modules["vllm.model_executor.utils"].set_weight_attrs = lambda w, attrs: None
+        sys.modules["vllm.platforms"].current_platform = _Platform()
+        sys.modules["vllm.utils"].LazyDict = LazyDict
+        layers = "vllm/model_executor/layers"
+        norm = _exec("vllm.model_executor.layers.layernorm", os.path.join(REF_ROOT, layers, "layernorm.py"))
+        act = _exec("vllm.model_executor.layers.activation", os.path.join(REF_ROOT, layers, "activation.py"))
+    finally:
+        for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+    _cached_layers = (norm.RMSNorm, act.SiluAndMul)
+    return _cached_layers
