@@ -139,3 +139,73 @@ def load_reference_layers():
         sys.modules.update(saved)
     _cached_layers = (norm.RMSNorm, act.SiluAndMul)
     return _cached_layers
+
+
+_cached_linear = None
+
+
+def load_reference_linear():
+    """The reference's own TP linear layers with its own AQLM method: ``layers/linear.py``,
+    ``parameter.py``, ``model_executor/utils.py``, ``quantization/base_config.py`` and
+    ``quantization/aqlm.py`` executed unmodified under stubs.  Returns a namespace with
+    ``linear`` and ``aqlm`` (the module objects) and ``set_tp(rank, world)``: the stubbed
+    ``vllm.distributed`` answers with that simulated rank, so every rank's sharded ``create_weights`` and
+    ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: calling
+    them raises - only construction and loading are meant to be used."""
+    global _cached_linear
+    if _cached_linear is not None:
+        return _cached_linear
+    if not available():
+        raise FileNotFoundError(f"reference not present under {REF_ROOT}")
+    state = {"rank": 0, "world": 1}
+    saved = {k: v for k, v in sys.modules.items() if k == "vllm" or k.startswith("vllm.")}
+    try:
+        for name in ("vllm", "vllm._custom_ops", "vllm.distributed", "vllm.logger", "vllm.platforms",
+                     "vllm.model_executor", "vllm.model_executor.layers",
+                     "vllm.model_executor.layers.quantization"):
+            sys.modules[name] = types.ModuleType(name)
+        sys.modules["vllm"]._custom_ops = sys.modules["vllm._custom_ops"]
+
+        def divide(a, b):                               # distributed/utils.py: exact division or assert
+            assert a % b == 0, f"{a} is not divisible by {b}"
+            return a // b
+
+        def no_collective(*a, **k):
+            raise RuntimeError("reference collectives are not available under the stub")
+
+        def split_tensor_along_last_dim(t, n, contiguous_split_chunks=False):
+            return torch.split(t, divide(t.size(-1), n), dim=-1)
+
+        dist = sys.modules["vllm.distributed"]
+        dist.divide = divide
+        dist.get_tensor_model_parallel_rank = lambda: state["rank"]
+        dist.get_tensor_model_parallel_world_size = lambda: state["world"]
+        dist.split_tensor_along_last_dim = split_tensor_along_last_dim
+        dist.tensor_model_parallel_all_gather = no_collective
+        dist.tensor_model_parallel_all_reduce = no_collective
+        import logging
+        sys.modules["vllm.logger"].init_logger = logging.getLogger
+
+        class _Platform:
+            def __getattr__(self, name):
+                if name.startswith("is_"):
+                    return lambda *a, **k: False
+                raise AttributeError(name)
+
+        sys.modules["vllm.platforms"].current_platform = _Platform()
+        me = os.path.join(REF_ROOT, "vllm/model_executor")
+        _exec("vllm.model_executor.utils", os.path.join(me, "utils.py"))
+        _exec("vllm.model_executor.layers.quantization.base_config", os.path.join(REF_ROOT, _Q, "base_config.py"))
+        _exec("vllm.model_executor.parameter", os.path.join(me, "parameter.py"))
+        linear = _exec("vllm.model_executor.layers.linear", os.path.join(me, "layers/linear.py"))
+        aqlm = _exec("vllm.model_executor.layers.quantization.aqlm", os.path.join(REF_ROOT, _Q, "aqlm.py"))
+    finally:
+        for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
+            del sys.modules[k]
+        sys.modules.update(saved)
+
+    def set_tp(rank: int, world: int):
+        state["rank"], state["world"] = rank, world
+
+    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, set_tp=set_tp)
+    return _cached_linear

@@ -1,0 +1,164 @@
+"""Sharded create_weights and the weight loaders against the REFERENCE's own linear.py + aqlm.py
+(SURVEY.md A13), every tensor-parallel rank simulated in one process.
+
+oracle/ref_loader.load_reference_linear() executes the reference's layers/linear.py, parameter.py,
+model_executor/utils.py, quantization/base_config.py and quantization/aqlm.py unmodified under stubs whose
+``vllm.distributed`` answers with a settable (rank, world).  The same full-size checkpoint tensors go
+through the reference layer's ``weight_loader`` and through ours; every parameter must come out with the
+same shape, dtype, attributes and bits.  Only where /root/reference exists (the build container): the
+gloo tests (tests/test_tp_gloo.py) cover the same logic against the oracle's arithmetic everywhere.
+"""
+import pytest
+import torch
+
+import vllm_pq_b200 as P
+from oracle import pq_oracle as O
+from oracle import ref_loader
+from vllm_pq_b200 import distributed as D
+
+pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present (GPU box)")
+
+FORMATS = [(8, 8, 1), (8, 8, 2), (16, 8, 1), (12, 16, 1)]
+HIDDEN, HEAD, HEADS, KV_HEADS, FFN = 256, 32, 8, 2, 512
+ATTRS = ("input_dim", "output_dim", "packed_dim", "pack_factor", "is_metadata", "output_partition_sizes", "ignore_warning")
+
+
+@pytest.fixture
+def tp(monkeypatch):
+    R = ref_loader.load_reference_linear()
+
+    def set_tp(rank, world):
+        R.set_tp(rank, world)
+        monkeypatch.setattr(D, "_TP_RANK", rank)
+        monkeypatch.setattr(D, "_TP_WORLD", world)
+    yield R, set_tp
+    R.set_tp(0, 1)
+
+
+def same_layer(ours, theirs, what):
+    mine, ref = dict(ours.named_parameters()), dict(theirs.named_parameters())
+    assert set(mine) == set(ref), what
+    for name, p in ref.items():
+        q = mine[name]
+        assert q.shape == p.shape and q.dtype == p.dtype, f"{what}.{name}: {tuple(q.shape)} {q.dtype} vs {tuple(p.shape)} {p.dtype}"
+        assert torch.equal(q.data.view(torch.int16) if q.dtype.is_floating_point else q.data,
+                           p.data.view(torch.int16) if p.dtype.is_floating_point else p.data), f"{what}.{name}"
+        for a in ATTRS:
+            assert getattr(q, a, None) == getattr(p, a, None), f"{what}.{name}.{a}"
+
+
+def fill_garbage(layer, seed):
+    g = torch.Generator().manual_seed(seed)
+    for p in layer.parameters():
+        if p.dtype.is_floating_point:
+            p.data.copy_(torch.randn(p.shape, generator=g))
+        else:
+            p.data.copy_(torch.randint(-100, 100, p.shape, generator=g))
+
+
+def build_pair(R, fmt, kind):
+    b, d, m = fmt
+    rcfg, ocfg = R.aqlm.AQLMConfig(d, b, m, 1), P.PQConfig(d, b, m, 1)
+    kw = dict(bias=True, params_dtype=torch.float16)
+    L = R.linear
+    if kind == "qkv":
+        return (P.QKVParallelLinear(HIDDEN, HEAD, HEADS, KV_HEADS, quant_config=ocfg, **kw),
+                L.QKVParallelLinear(HIDDEN, HEAD, HEADS, KV_HEADS, quant_config=rcfg, **kw))
+    if kind == "gate_up":
+        return (P.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], quant_config=ocfg, **kw),
+                L.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], quant_config=rcfg, **kw))
+    if kind == "column":
+        return (P.ColumnParallelLinear(HIDDEN, FFN, quant_config=ocfg, **kw),
+                L.ColumnParallelLinear(HIDDEN, FFN, quant_config=rcfg, **kw))
+    if kind == "row":
+        return (P.RowParallelLinear(FFN, HIDDEN, quant_config=ocfg, **kw),
+                L.RowParallelLinear(FFN, HIDDEN, quant_config=rcfg, **kw))
+    return (P.ReplicatedLinear(HIDDEN, FFN, quant_config=ocfg, **kw),
+            L.ReplicatedLinear(HIDDEN, FFN, quant_config=rcfg, **kw))
+
+
+def load_both(ours, theirs, tensors, shard_id=None):
+    for layer in (ours, theirs):
+        params = dict(layer.named_parameters())
+        for key, t in tensors.items():
+            if shard_id is None:
+                params[key].weight_loader(params[key], t.clone())
+            else:
+                params[key].weight_loader(params[key], t.clone(), shard_id)
+
+
+def case(n, k, fmt, seed):
+    b, d, m = fmt
+    c = O.make_case([n], k, b, d, m, t=1, dtype=torch.float16, seed=seed, bias=True)
+    return {key: c[key] for key in ("codes", "codebooks", "scales", "bias")}
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("fmt", FORMATS, ids=["8x8x1", "8x8x2", "16x8x1", "12x16x1"])
+def test_every_rank_loads_what_the_reference_loads(tp, fmt, world):
+    R, set_tp = tp
+    b, d, m = fmt
+    for rank in range(world):
+        set_tp(rank, world)
+        # q / k / v and gate / up as separate checkpoint tensors (llama.py:371-378)
+        ours, theirs = build_pair(R, fmt, "qkv")
+        fill_garbage(ours, 1); fill_garbage(theirs, 2)
+        for sid, n in (("q", HEADS * HEAD), ("k", KV_HEADS * HEAD), ("v", KV_HEADS * HEAD)):
+            load_both(ours, theirs, case(n, HIDDEN, fmt, 20 + ord(sid)), sid)
+        same_layer(ours, theirs, f"qkv rank {rank}/{world}")
+        assert list(ours.output_partition_sizes) == list(theirs.output_partition_sizes)
+        assert (ours.num_heads, ours.num_kv_heads, ours.num_kv_head_replicas) == \
+               (theirs.num_heads, theirs.num_kv_heads, theirs.num_kv_head_replicas)
+
+        ours, theirs = build_pair(R, fmt, "gate_up")
+        fill_garbage(ours, 3); fill_garbage(theirs, 4)
+        for sid in (0, 1):
+            load_both(ours, theirs, case(FFN, HIDDEN, fmt, 30 + sid), sid)
+        same_layer(ours, theirs, f"gate_up rank {rank}/{world}")
+
+        for kind, n, k in (("column", FFN, HIDDEN), ("row", HIDDEN, FFN), ("replicated", FFN, HIDDEN)):
+            if kind == "row" and (FFN // d) % world:
+                continue
+            ours, theirs = build_pair(R, fmt, kind)
+            fill_garbage(ours, 5); fill_garbage(theirs, 6)
+            load_both(ours, theirs, case(n, k, fmt, 40))
+            same_layer(ours, theirs, f"{kind} rank {rank}/{world}")
+            if kind == "row":
+                assert ours.input_size_per_partition == theirs.input_size_per_partition
+                # the bias is added by rank 0 only (linear.py:1206-1208)
+                assert ours.skip_bias_add == theirs.skip_bias_add
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_fused_on_disk_checkpoints(tp, world):
+    """qkv_proj / gate_up_proj already concatenated in the checkpoint: loaded_shard_id is None
+    (linear.py:506-559, 890-944).  The codes and scales are split per shard by both; the codebooks
+    (is_metadata, no output_dim) are copied whole."""
+    R, set_tp = tp
+    fmt = (8, 8, 1)
+    for rank in range(world):
+        set_tp(rank, world)
+        ours, theirs = build_pair(R, fmt, "qkv")
+        c = O.make_case([HEADS * HEAD, KV_HEADS * HEAD, KV_HEADS * HEAD], HIDDEN, 8, 8, 1, t=1, dtype=torch.float16, seed=50, bias=True)
+        load_both(ours, theirs, {key: c[key] for key in ("codes", "codebooks", "scales", "bias")})
+        same_layer(ours, theirs, f"fused qkv rank {rank}/{world}")
+        ours, theirs = build_pair(R, fmt, "gate_up")
+        c = O.make_case([FFN, FFN], HIDDEN, 8, 8, 1, t=1, dtype=torch.float16, seed=51, bias=True)
+        load_both(ours, theirs, {key: c[key] for key in ("codes", "codebooks", "scales", "bias")})
+        same_layer(ours, theirs, f"fused gate_up rank {rank}/{world}")
+
+
+def test_construction_errors_match(tp):
+    R, set_tp = tp
+    set_tp(0, 3)
+    cfg_r, cfg_o = R.aqlm.AQLMConfig(8, 8, 1, 1), P.PQConfig(8, 8, 1, 1)
+    for make in (lambda L, c: L.ColumnParallelLinear(HIDDEN, 100, bias=False, params_dtype=torch.float16, quant_config=c),
+                 lambda L, c: L.RowParallelLinear(FFN, HIDDEN, bias=False, params_dtype=torch.float16, quant_config=c)):
+        with pytest.raises((AssertionError, ValueError)):
+            make(R.linear, cfg_r)
+        with pytest.raises((AssertionError, ValueError)):
+            make(P, cfg_o)
+    set_tp(0, 1)
+    for cfg, mod in ((cfg_r, R.linear), (cfg_o, P)):
+        with pytest.raises(ValueError):                  # aqlm.py:238-239: half precision only
+            mod.ColumnParallelLinear(HIDDEN, FFN, bias=False, params_dtype=torch.float32, quant_config=cfg)
