@@ -199,6 +199,7 @@ def load_reference_linear():
         _exec("vllm.model_executor.parameter", os.path.join(me, "parameter.py"))
         linear = _exec("vllm.model_executor.layers.linear", os.path.join(me, "layers/linear.py"))
         aqlm = _exec("vllm.model_executor.layers.quantization.aqlm", os.path.join(REF_ROOT, _Q, "aqlm.py"))
+        mixtral = _exec_mixtral_quant(me, dist, state)
     finally:
         for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
             del sys.modules[k]
@@ -207,5 +208,57 @@ def load_reference_linear():
     def set_tp(rank: int, world: int):
         state["rank"], state["world"] = rank, world
 
-    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, set_tp=set_tp)
+    def set_all_reduce(fn):
+        """What the stubbed tensor_model_parallel_all_reduce does from now on (None: raise)."""
+        state["all_reduce"] = fn
+
+    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, mixtral=mixtral, set_tp=set_tp,
+                                           set_all_reduce=set_all_reduce)
     return _cached_linear
+
+
+class _AnyModule(types.ModuleType):
+    """A stub module whose every attribute is an empty placeholder class: enough for the
+    ``from x import Name`` lines and type annotations of code paths that are never run."""
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        cls = type(name, (), {})
+        setattr(self, name, cls)
+        return cls
+
+
+def _exec_mixtral_quant(me: str, dist, state):
+    """models/mixtral_quant.py (the reference's non-fused quantised Mixtral, the path an AQLM Mixtral
+    takes) for its MixtralMLP / MixtralMoE classes.  Called inside load_reference_linear()'s stub
+    environment; attention, rotary, sampler, embeddings ... are placeholders, never constructed."""
+    def all_reduce(t):
+        if state.get("all_reduce") is None:
+            raise RuntimeError("reference collectives are not available under the stub")
+        return state["all_reduce"](t)
+
+    dist.tensor_model_parallel_all_reduce = all_reduce
+    dist.get_pp_group = lambda: None
+    for name in ("vllm.attention", "vllm.config", "vllm.sequence", "vllm.model_executor.custom_op",
+                 "vllm.model_executor.layers.logits_processor", "vllm.model_executor.layers.rotary_embedding",
+                 "vllm.model_executor.layers.sampler", "vllm.model_executor.layers.vocab_parallel_embedding",
+                 "vllm.model_executor.model_loader", "vllm.model_executor.model_loader.weight_utils",
+                 "vllm.model_executor.sampling_metadata", "vllm.model_executor.models",
+                 "vllm.model_executor.models.interfaces", "vllm.model_executor.models.utils"):
+        sys.modules[name] = _AnyModule(name)
+    sys.modules["vllm.model_executor.models"].__path__ = []         # a package, for the relative imports
+
+    class CustomOp(torch.nn.Module):
+        @classmethod
+        def register(cls, name):
+            return lambda op_cls: op_cls
+
+        def forward(self, *args, **kwargs):
+            return self.forward_native(*args, **kwargs)
+
+    sys.modules["vllm.model_executor.custom_op"].CustomOp = CustomOp
+    base = sys.modules["vllm.model_executor.layers.quantization.base_config"]
+    sys.modules["vllm.model_executor.layers.quantization"].QuantizationConfig = base.QuantizationConfig
+    _exec("vllm.model_executor.layers.layernorm", os.path.join(me, "layers/layernorm.py"))
+    return _exec("vllm.model_executor.models.mixtral_quant", os.path.join(me, "models/mixtral_quant.py"))

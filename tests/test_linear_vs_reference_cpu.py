@@ -162,3 +162,67 @@ def test_construction_errors_match(tp):
     for cfg, mod in ((cfg_r, R.linear), (cfg_o, P)):
         with pytest.raises(ValueError):                  # aqlm.py:238-239: half precision only
             mod.ColumnParallelLinear(HIDDEN, FFN, bias=False, params_dtype=torch.float32, quant_config=cfg)
+
+
+# ---- the quantised Mixtral block against the reference's own mixtral_quant.py ----------
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 3)], ids=["8x8x1", "8x8x3"])
+def test_mixtral_block_matches_reference_forward(tp, monkeypatch, fmt, world):
+    """MixtralMoE.forward of the reference (mixtral_quant.py:133-160) runs on the CPU for formats outside
+    its two kernel formats: its AQLM ``apply`` falls to generic_dequantize_gemm (aqlm.py:366-374).  Our
+    block with ``pq::gemm`` replaced by the oracle's restatement of that function must give the same
+    values (bit for bit, up to the sign of zeros): routing, expert split between ranks, weighting,
+    accumulation order, skipped experts."""
+    from transformers import MixtralConfig
+
+    from vllm_pq_b200 import _custom_ops as ops
+    R, set_tp = tp
+    b, d, m = fmt
+    hidden, ffn, n_exp, top_k = 128, 256, 4, 2
+    monkeypatch.setattr(ops, "pq_gemm", lambda x, codes, codebooks, scales, parts, bias, algo=0:
+                        O.generic_dequantize_gemm(x, codes, codebooks, scales, parts, bias))
+    R.set_all_reduce(lambda t: t)                        # each simulated rank's partial sum
+    monkeypatch.setattr(D, "tensor_model_parallel_all_reduce", lambda t: t)
+    import vllm_pq_b200.moe as moe_mod
+    monkeypatch.setattr(moe_mod, "tensor_model_parallel_all_reduce", lambda t: t)
+    gen = torch.Generator().manual_seed(3)
+    gate = torch.randn(n_exp, hidden, generator=gen).half()
+    weights = {}
+    for e in range(n_exp):
+        for name, n, k in (("w1", ffn, hidden), ("w3", ffn, hidden), ("w2", hidden, ffn)):
+            c = O.make_case([n], k, b, d, m, dtype=torch.float16, seed=200 + 10 * e + ord(name[1]))
+            c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).half()
+            weights[(e, name)] = c
+    try:
+        for rank in range(world):
+            set_tp(rank, world)
+            torch.set_default_dtype(torch.float16)
+            try:
+                theirs = R.mixtral.MixtralMoE(MixtralConfig(hidden_size=hidden, intermediate_size=ffn, num_local_experts=n_exp,
+                                                            num_experts_per_tok=top_k), R.aqlm.AQLMConfig(d, b, m, 1))
+            finally:
+                torch.set_default_dtype(torch.float32)
+            ours = P.PQMixtralMoE(n_exp, top_k, hidden, ffn, params_dtype=torch.float16, quant_config=P.PQConfig(d, b, m, 1))
+            assert ours.expert_indicies == theirs.expert_indicies
+            assert [e is None for e in ours.experts] == [e is None for e in theirs.experts]
+            theirs.gate.weight.data.copy_(gate)
+            ours.gate_weight.data.copy_(gate)
+            for e in ours.expert_indicies:
+                for name in ("w1", "w2", "w3"):
+                    for layer in (getattr(ours.experts[e], name), getattr(theirs.experts[e], name)):
+                        for key in ("codes", "codebooks", "scales"):
+                            p = getattr(layer, key)
+                            p.weight_loader(p, weights[(e, name)][key])
+            for t in (1, 5, 40):
+                x = torch.randn(t, hidden, generator=gen).half()
+                with torch.no_grad():
+                    y_ref = theirs(x.clone())
+                    y = ours(x.clone())
+                assert y.shape == y_ref.shape and y.dtype == y_ref.dtype
+                # equal as numbers: identical bits except the sign of a zero - an expert no token chose is
+                # skipped here (+0) and multiplied by a zero weight there (-0 where its output is negative)
+                assert torch.equal(y, y_ref), f"rank {rank}/{world}, {t} tokens"
+                nz = y_ref != 0
+                assert torch.equal(y.view(torch.int16)[nz], y_ref.view(torch.int16)[nz])
+    finally:
+        R.set_all_reduce(None)

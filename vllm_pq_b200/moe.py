@@ -73,7 +73,7 @@ class PQMixtralMoE(nn.Module):
         # which local experts got any token: one small device-to-host read per step at decode buys
         # skipping the (num_local - top_k) experts whose weight is exactly zero for every token
         used = None
-        if num_tokens <= 8 and not torch.cuda.is_current_stream_capturing():
+        if num_tokens <= 8 and not (hidden_states.is_cuda and torch.cuda.is_current_stream_capturing()):
             used = set(selected_experts.flatten().tolist())
         for expert_idx in self.expert_indicies:
             if used is not None and expert_idx not in used:
