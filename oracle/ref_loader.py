@@ -150,8 +150,9 @@ def load_reference_linear():
     ``quantization/aqlm.py`` executed unmodified under stubs.  Returns a namespace with
     ``linear`` and ``aqlm`` (the module objects) and ``set_tp(rank, world)``: the stubbed
     ``vllm.distributed`` answers with that simulated rank, so every rank's sharded ``create_weights`` and
-    ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: calling
-    them raises - only construction and loading are meant to be used."""
+    ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: the
+    all-gather raises, the all-reduce raises unless ``set_all_reduce(fn)`` installed a stand-in (the
+    identity, to look at one simulated rank's partial result)."""
     global _cached_linear
     if _cached_linear is not None:
         return _cached_linear
@@ -173,16 +174,21 @@ def load_reference_linear():
         def no_collective(*a, **k):
             raise RuntimeError("reference collectives are not available under the stub")
 
-        def split_tensor_along_last_dim(t, n, contiguous_split_chunks=False):
-            return torch.split(t, divide(t.size(-1), n), dim=-1)
+        def split_tensor_along_last_dim(tensor, num_partitions, contiguous_split_chunks=False):
+            return torch.split(tensor, divide(tensor.size(-1), num_partitions), dim=-1)
 
         dist = sys.modules["vllm.distributed"]
         dist.divide = divide
         dist.get_tensor_model_parallel_rank = lambda: state["rank"]
         dist.get_tensor_model_parallel_world_size = lambda: state["world"]
         dist.split_tensor_along_last_dim = split_tensor_along_last_dim
+        def all_reduce(t):                              # set_all_reduce(fn) below; None: raise
+            if state.get("all_reduce") is None:
+                return no_collective()
+            return state["all_reduce"](t)
+
         dist.tensor_model_parallel_all_gather = no_collective
-        dist.tensor_model_parallel_all_reduce = no_collective
+        dist.tensor_model_parallel_all_reduce = all_reduce
         import logging
         sys.modules["vllm.logger"].init_logger = logging.getLogger
 
@@ -233,12 +239,6 @@ def _exec_mixtral_quant(me: str, dist, state):
     """models/mixtral_quant.py (the reference's non-fused quantised Mixtral, the path an AQLM Mixtral
     takes) for its MixtralMLP / MixtralMoE classes.  Called inside load_reference_linear()'s stub
     environment; attention, rotary, sampler, embeddings ... are placeholders, never constructed."""
-    def all_reduce(t):
-        if state.get("all_reduce") is None:
-            raise RuntimeError("reference collectives are not available under the stub")
-        return state["all_reduce"](t)
-
-    dist.tensor_model_parallel_all_reduce = all_reduce
     dist.get_pp_group = lambda: None
     for name in ("vllm.attention", "vllm.config", "vllm.sequence", "vllm.model_executor.custom_op",
                  "vllm.model_executor.layers.logits_processor", "vllm.model_executor.layers.rotary_embedding",

@@ -226,3 +226,75 @@ def test_mixtral_block_matches_reference_forward(tp, monkeypatch, fmt, world):
                 assert torch.equal(y.view(torch.int16)[nz], y_ref.view(torch.int16)[nz])
     finally:
         R.set_all_reduce(None)
+
+
+# ---- layer forward against the reference's own forward (generic formats run on the CPU there) ---------
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (4, 8, 2)], ids=["8x8x1", "4x8x2"])
+def test_layer_forward_matches_reference_forward(tp, monkeypatch, fmt, world):
+    """ColumnParallel / Merged / QKV / RowParallel / Replicated ``forward`` (linear.py:285-295,410-435,
+    1193-1221): what goes to ``apply`` (the input chunk of a non-parallel row input, bias on rank 0 only,
+    skip_bias_add) and what comes back (output, output_bias).  ``pq::gemm`` is replaced by the oracle's
+    generic_dequantize_gemm - bit-equal to the reference's (tests/test_oracle_golden.py) - and the
+    all-reduce by the identity on both sides, so every simulated rank's partial result is compared."""
+    from vllm_pq_b200 import _custom_ops as ops
+    R, set_tp = tp
+    b, d, m = fmt
+    monkeypatch.setattr(ops, "pq_gemm", lambda x, codes, codebooks, scales, parts, bias, algo=0:
+                        O.generic_dequantize_gemm(x, codes, codebooks, scales, parts, bias))
+    monkeypatch.setattr(D, "tensor_model_parallel_all_reduce", lambda t: t)
+    import vllm_pq_b200.linear as lin_mod
+    monkeypatch.setattr(lin_mod, "tensor_model_parallel_all_reduce", lambda t: t)
+    R.set_all_reduce(lambda t: t)
+    gen = torch.Generator().manual_seed(5)
+    rcfg, ocfg = R.aqlm.AQLMConfig(d, b, m, 1), P.PQConfig(d, b, m, 1)
+    kw = dict(params_dtype=torch.float16)
+
+    def check(ours, theirs, x, what):
+        with torch.no_grad():
+            y_ref, b_ref = theirs(x.clone())
+            y, b_out = ours(x.clone())
+        assert y.shape == y_ref.shape and torch.equal(y.view(torch.int16), y_ref.view(torch.int16)), what
+        assert (b_out is None) == (b_ref is None), what
+        if b_ref is not None:
+            assert torch.equal(b_out, b_ref), what
+
+    try:
+        for rank in range(world):
+            set_tp(rank, world)
+            x = torch.randn(2, 3, HIDDEN, generator=gen).half()
+            xr_full = torch.randn(2, 3, FFN, generator=gen).half()
+            for bias, skip in ((True, False), (True, True), (False, False)):
+                tag = f"rank {rank}/{world} bias={bias} skip_bias_add={skip}"
+                pairs = [
+                    ("qkv", P.QKVParallelLinear(HIDDEN, HEAD, HEADS, KV_HEADS, bias=bias, skip_bias_add=skip, quant_config=ocfg, **kw),
+                     R.linear.QKVParallelLinear(HIDDEN, HEAD, HEADS, KV_HEADS, bias=bias, skip_bias_add=skip, quant_config=rcfg, **kw), x),
+                    ("gate_up", P.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], bias=bias, skip_bias_add=skip, quant_config=ocfg, **kw),
+                     R.linear.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], bias=bias, skip_bias_add=skip, quant_config=rcfg, **kw), x),
+                    ("replicated", P.ReplicatedLinear(HIDDEN, FFN, bias=bias, skip_bias_add=skip, quant_config=ocfg, **kw),
+                     R.linear.ReplicatedLinear(HIDDEN, FFN, bias=bias, skip_bias_add=skip, quant_config=rcfg, **kw), x),
+                ]
+                for parallel_in in (True, False):
+                    xr = xr_full[..., rank * (FFN // world):(rank + 1) * (FFN // world)].contiguous() if parallel_in else xr_full
+                    pairs.append((f"row(input_is_parallel={parallel_in})",
+                                  P.RowParallelLinear(FFN, HIDDEN, bias=bias, skip_bias_add=skip, input_is_parallel=parallel_in,
+                                                      quant_config=ocfg, **kw),
+                                  R.linear.RowParallelLinear(FFN, HIDDEN, bias=bias, skip_bias_add=skip,
+                                                             input_is_parallel=parallel_in, quant_config=rcfg, **kw), xr))
+                for name, ours, theirs, xin in pairs:
+                    seeds = {"qkv": 61, "gate_up": 62, "replicated": 63}.get(name, 64)
+                    fused = {"qkv": [("q", HEADS * HEAD), ("k", KV_HEADS * HEAD), ("v", KV_HEADS * HEAD)],
+                             "gate_up": [(0, FFN), (1, FFN)]}.get(name)
+                    if fused:
+                        for i, (sid, n) in enumerate(fused):
+                            c = case(n, HIDDEN, fmt, seeds * 10 + i)
+                            c["codebooks"] = (c["codebooks"].float() / (HIDDEN * m) ** 0.5).half()
+                            load_both(ours, theirs, {k_: v for k_, v in c.items() if k_ != "bias" or bias}, sid)
+                    else:
+                        n, k = (HIDDEN, FFN) if name.startswith("row") else (FFN, HIDDEN)
+                        c = case(n, k, fmt, seeds)
+                        c["codebooks"] = (c["codebooks"].float() / (k * m) ** 0.5).half()
+                        load_both(ours, theirs, {k_: v for k_, v in c.items() if k_ != "bias" or bias})
+                    check(ours, theirs, xin, f"{name} {tag}")
+    finally:
+        R.set_all_reduce(None)
