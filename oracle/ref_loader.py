@@ -148,7 +148,8 @@ def load_reference_linear():
     """The reference's own TP linear layers with its own AQLM method: ``layers/linear.py``,
     ``parameter.py``, ``model_executor/utils.py``, ``quantization/base_config.py`` and
     ``quantization/aqlm.py`` executed unmodified under stubs.  Returns a namespace with
-    ``linear`` and ``aqlm`` (the module objects) and ``set_tp(rank, world)``: the stubbed
+    ``linear``, ``aqlm``, ``vocab`` (layers/vocab_parallel_embedding.py) and ``mixtral``
+    (models/mixtral_quant.py) - the module objects - and ``set_tp(rank, world)``: the stubbed
     ``vllm.distributed`` answers with that simulated rank, so every rank's sharded ``create_weights`` and
     ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: the
     all-gather raises, the all-reduce raises unless ``set_all_reduce(fn)`` installed a stand-in (the
@@ -193,6 +194,8 @@ def load_reference_linear():
         sys.modules["vllm.logger"].init_logger = logging.getLogger
 
         class _Platform:
+            simple_compile_backend = "eager"            # vocab_parallel_embedding.py:138 (torch.compile)
+
             def __getattr__(self, name):
                 if name.startswith("is_"):
                     return lambda *a, **k: False
@@ -205,6 +208,8 @@ def load_reference_linear():
         _exec("vllm.model_executor.parameter", os.path.join(me, "parameter.py"))
         linear = _exec("vllm.model_executor.layers.linear", os.path.join(me, "layers/linear.py"))
         aqlm = _exec("vllm.model_executor.layers.quantization.aqlm", os.path.join(REF_ROOT, _Q, "aqlm.py"))
+        vocab = _exec("vllm.model_executor.layers.vocab_parallel_embedding",
+                      os.path.join(me, "layers/vocab_parallel_embedding.py"))
         mixtral = _exec_mixtral_quant(me, dist, state)
     finally:
         for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
@@ -218,7 +223,7 @@ def load_reference_linear():
         """What the stubbed tensor_model_parallel_all_reduce does from now on (None: raise)."""
         state["all_reduce"] = fn
 
-    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, mixtral=mixtral, set_tp=set_tp,
+    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, vocab=vocab, mixtral=mixtral, set_tp=set_tp,
                                            set_all_reduce=set_all_reduce)
     return _cached_linear
 
@@ -242,7 +247,7 @@ def _exec_mixtral_quant(me: str, dist, state):
     dist.get_pp_group = lambda: None
     for name in ("vllm.attention", "vllm.config", "vllm.sequence", "vllm.model_executor.custom_op",
                  "vllm.model_executor.layers.logits_processor", "vllm.model_executor.layers.rotary_embedding",
-                 "vllm.model_executor.layers.sampler", "vllm.model_executor.layers.vocab_parallel_embedding",
+                 "vllm.model_executor.layers.sampler",
                  "vllm.model_executor.model_loader", "vllm.model_executor.model_loader.weight_utils",
                  "vllm.model_executor.sampling_metadata", "vllm.model_executor.models",
                  "vllm.model_executor.models.interfaces", "vllm.model_executor.models.utils"):

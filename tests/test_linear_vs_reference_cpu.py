@@ -298,3 +298,89 @@ def test_layer_forward_matches_reference_forward(tp, monkeypatch, fmt, world):
                     check(ours, theirs, xin, f"{name} {tag}")
     finally:
         R.set_all_reduce(None)
+
+
+# ---- vocabulary layers against the reference's own vocab_parallel_embedding.py ---------
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("vocab", [100, 320, 32000])
+def test_vocab_layers_match_reference(tp, monkeypatch, vocab, world):
+    """The reference keeps its vocabulary layers dense under AQLM (aqlm.py:213-217), but the classes take
+    any method that implements ``embedding`` (vocab_parallel_embedding.py:229-246).  Here they get the
+    reference's AQLM method plus an ``embedding`` that looks rows up in the reference's own
+    dequantize_weight, so padding, shard ranges, ``create_weights``, ``weight_loader`` (zero padding rows)
+    and the masked lookup of ``forward`` are the reference's code; ours runs with ``pq::embedding`` /
+    ``pq::gemm`` replaced by the oracle."""
+    import torch.nn.functional as F
+
+    from vllm_pq_b200 import _custom_ops as ops
+    from vllm_pq_b200 import embedding as emb_mod
+    R, set_tp = tp
+    b, d, m, hidden = 8, 8, 1, 64
+
+    class Method(R.aqlm.AQLMLinearMethod):
+        def embedding(self, layer, input_):
+            w = R.aqlm.dequantize_weight(R.aqlm.unpack_int_data(layer.codes, b), layer.codebooks, layer.scales)
+            return F.embedding(input_, w)
+
+    class Config(R.aqlm.AQLMConfig):
+        def get_quant_method(self, layer, prefix):
+            return Method(self)
+
+    def cpu_embedding(ids, codes, codebooks, scales):
+        w = O.dequantize_partitions(codes, codebooks, [codes.shape[0]], scales)
+        out = torch.zeros(ids.shape + (w.shape[1],), dtype=w.dtype)
+        ok = (ids >= 0) & (ids < w.shape[0])
+        out[ok] = w[ids[ok]]
+        return out
+
+    monkeypatch.setattr(ops, "pq_embedding", cpu_embedding)
+    monkeypatch.setattr(ops, "pq_gemm", lambda x, codes, codebooks, scales, parts, bias, algo=0:
+                        O.generic_dequantize_gemm(x, codes, codebooks, scales, parts, bias))
+    monkeypatch.setattr(emb_mod, "tensor_model_parallel_all_reduce", lambda t: t)
+    R.set_all_reduce(lambda t: t)
+    c = O.make_case([vocab], hidden, b, d, m, t=3, dtype=torch.float16, seed=77, bias=True)
+    gen = torch.Generator().manual_seed(8)
+    ids = torch.randint(0, vocab, (2, 9), generator=gen)
+    ids[0, :3] = torch.tensor([0, vocab - 1, vocab // 2])
+    try:
+        for rank in range(world):
+            set_tp(rank, world)
+            kw = dict(params_dtype=torch.float16)
+            for cls_o, cls_r in ((P.VocabParallelEmbedding, R.vocab.VocabParallelEmbedding),
+                                 (P.ParallelLMHead, R.vocab.ParallelLMHead)):
+                extra = dict(bias=True) if cls_o is P.ParallelLMHead else {}
+                ours = cls_o(vocab, hidden, quant_config=P.PQConfig(d, b, m, 1, lm_head_quantized=True), **extra, **kw)
+                theirs = cls_r(vocab, hidden, quant_config=Config(d, b, m, 1), **extra, **kw)
+                fill_garbage(ours, 1); fill_garbage(theirs, 2)
+                # vocab_parallel_embedding.py:376-380 reads `param.packed_factor` inside an assert where plain
+                # Parameters carry `pack_factor` (the AQLM scales: packed_dim == output_dim, factor 1) - a path
+                # the reference never took, its AQLM vocabulary layers being dense.  Give it the name it reads.
+                theirs.scales.packed_factor = theirs.scales.pack_factor
+                tensors = {k: c[k] for k in ("codes", "codebooks", "scales")}
+                if extra:
+                    tensors["bias"] = c["bias"]
+                load_both(ours, theirs, tensors)
+                same_layer(ours, theirs, f"{cls_o.__name__} rank {rank}/{world}")
+                assert ours.num_embeddings_padded == theirs.num_embeddings_padded
+                assert ours.num_embeddings_per_partition == theirs.num_embeddings_per_partition
+                si = theirs.shard_indices                    # the reference clamps its range to the real vocabulary
+                assert (min(ours.vocab_start, vocab), min(ours.vocab_end, vocab)) == \
+                       (si.org_vocab_start_index, si.org_vocab_end_index)
+                if cls_o is P.VocabParallelEmbedding:
+                    with torch.no_grad():
+                        y_ref, y = theirs(ids.clone()), ours(ids.clone())
+                    assert torch.equal(y, y_ref), f"lookup rank {rank}/{world}"      # +-0 in masked rows
+                    nz = y_ref != 0
+                    assert torch.equal(y.view(torch.int16)[nz], y_ref.view(torch.int16)[nz])
+                else:
+                    with pytest.raises(RuntimeError):
+                        ours(ids)
+                    with pytest.raises(RuntimeError):
+                        theirs(ids)
+                    # logits_processor.py:_get_logits: lm_head.quant_method.apply(lm_head, h, bias)
+                    with torch.no_grad():
+                        lg_ref = theirs.quant_method.apply(theirs, c["x"], bias=theirs.bias)
+                        lg = ours.compute_logits(c["x"])
+                    assert torch.equal(lg.view(torch.int16), lg_ref.view(torch.int16))
+    finally:
+        R.set_all_reduce(None)
