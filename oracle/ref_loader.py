@@ -149,7 +149,8 @@ def load_reference_linear():
     ``parameter.py``, ``model_executor/utils.py``, ``quantization/base_config.py`` and
     ``quantization/aqlm.py`` executed unmodified under stubs.  Returns a namespace with
     ``linear``, ``aqlm``, ``vocab`` (layers/vocab_parallel_embedding.py) and ``mixtral``
-    (models/mixtral_quant.py) - the module objects - and ``set_tp(rank, world)``: the stubbed
+    (models/mixtral_quant.py), ``registry`` (quantization/__init__.py) and ``base_config`` - the module
+    objects - and ``set_tp(rank, world)``: the stubbed
     ``vllm.distributed`` answers with that simulated rank, so every rank's sharded ``create_weights`` and
     ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: the
     all-gather raises, the all-reduce raises unless ``set_all_reduce(fn)`` installed a stand-in (the
@@ -204,10 +205,12 @@ def load_reference_linear():
         sys.modules["vllm.platforms"].current_platform = _Platform()
         me = os.path.join(REF_ROOT, "vllm/model_executor")
         _exec("vllm.model_executor.utils", os.path.join(me, "utils.py"))
-        _exec("vllm.model_executor.layers.quantization.base_config", os.path.join(REF_ROOT, _Q, "base_config.py"))
+        sys_base = _exec("vllm.model_executor.layers.quantization.base_config",
+                         os.path.join(REF_ROOT, _Q, "base_config.py"))
         _exec("vllm.model_executor.parameter", os.path.join(me, "parameter.py"))
         linear = _exec("vllm.model_executor.layers.linear", os.path.join(me, "layers/linear.py"))
         aqlm = _exec("vllm.model_executor.layers.quantization.aqlm", os.path.join(REF_ROOT, _Q, "aqlm.py"))
+        registry = _exec("vllm.model_executor.layers.quantization", os.path.join(REF_ROOT, _Q, "__init__.py"))
         vocab = _exec("vllm.model_executor.layers.vocab_parallel_embedding",
                       os.path.join(me, "layers/vocab_parallel_embedding.py"))
         mixtral = _exec_mixtral_quant(me, dist, state)
@@ -223,7 +226,8 @@ def load_reference_linear():
         """What the stubbed tensor_model_parallel_all_reduce does from now on (None: raise)."""
         state["all_reduce"] = fn
 
-    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, vocab=vocab, mixtral=mixtral, set_tp=set_tp,
+    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, vocab=vocab, mixtral=mixtral, registry=registry,
+                                           base_config=sys_base, set_tp=set_tp,
                                            set_all_reduce=set_all_reduce)
     return _cached_linear
 

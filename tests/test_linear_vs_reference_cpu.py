@@ -384,3 +384,63 @@ def test_vocab_layers_match_reference(tp, monkeypatch, vocab, world):
                     assert torch.equal(lg.view(torch.int16), lg_ref.view(torch.int16))
     finally:
         R.set_all_reduce(None)
+
+
+# ---- the drop-in: OUR method behind the REFERENCE's plugin API, inside the reference's own layers -------
+def test_pq_method_plugs_into_the_reference_tree(tp, monkeypatch):
+    """What INTEGRATION.md tells a maintainer to do, done against the reference's real modules:
+    ``make_classes`` mounts the PQ config / method bodies on the reference's QuantizationConfig and
+    LinearMethodBase, ``register_quantization_config`` (quantization/__init__.py:39-73) registers the
+    result, and the reference's own QKV / merged / row-parallel layers build, load (their loaders) and
+    run (their forward) with it - giving the parameters and, with ``pq::gemm`` replaced by the oracle,
+    the outputs that the reference's AQLM method gives in the same layers."""
+    from vllm_pq_b200 import _custom_ops as ops
+    from vllm_pq_b200.pq import make_classes
+    R, set_tp = tp
+    cfg_cls, method_cls = make_classes(R.base_config.QuantizationConfig, R.linear.LinearMethodBase,
+                                       lambda layer: isinstance(layer, R.linear.LinearBase), name="pq")
+    assert issubclass(cfg_cls, R.base_config.QuantizationConfig) and issubclass(method_cls, R.linear.LinearMethodBase)
+    if "pq" not in R.registry.QUANTIZATION_METHODS:
+        assert R.registry.register_quantization_config("pq")(cfg_cls) is cfg_cls
+    assert "pq" in R.registry.QUANTIZATION_METHODS and "pq" in R.registry._CUSTOMIZED_METHOD_TO_QUANT_CONFIG
+    with pytest.raises(ValueError, match="already exists"):
+        R.registry.register_quantization_config("pq")(cfg_cls)
+    with pytest.raises(ValueError, match="already exists"):
+        R.registry.register_quantization_config("aqlm")(cfg_cls)
+    hf = {"in_group_size": 8, "nbits_per_codebook": 8, "num_codebooks": 1, "out_group_size": 1}
+    pq_cfg, aqlm_cfg = cfg_cls.from_config(dict(hf)), R.aqlm.AQLMConfig.from_config(dict(hf))
+    assert pq_cfg.get_name() == "pq" and cfg_cls.get_config_filenames() == R.aqlm.AQLMConfig.get_config_filenames()
+    assert pq_cfg.get_quant_method(torch.nn.Linear(8, 8), prefix="") is None          # aqlm.py:213-217
+
+    monkeypatch.setattr(ops, "pq_gemm", lambda x, codes, codebooks, scales, parts, bias, algo=0:
+                        O.generic_dequantize_gemm(x, codes, codebooks, scales, parts, bias))
+    R.set_all_reduce(lambda t: t)
+    gen = torch.Generator().manual_seed(12)
+    L = R.linear
+    try:
+        for world in (1, 2, 4):
+            for rank in range(world):
+                set_tp(rank, world)
+                kw = dict(bias=True, params_dtype=torch.float16)
+                layers = [
+                    (lambda c: L.QKVParallelLinear(HIDDEN, HEAD, HEADS, KV_HEADS, quant_config=c, **kw),
+                     [("q", HEADS * HEAD), ("k", KV_HEADS * HEAD), ("v", KV_HEADS * HEAD)], HIDDEN, HIDDEN),
+                    (lambda c: L.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], quant_config=c, **kw),
+                     [(0, FFN), (1, FFN)], HIDDEN, HIDDEN),
+                    (lambda c: L.RowParallelLinear(FFN, HIDDEN, quant_config=c, **kw), [(None, HIDDEN)], FFN, FFN // world),
+                ]
+                for make, shards, k, k_in in layers:
+                    with_pq, with_aqlm = make(pq_cfg), make(aqlm_cfg)
+                    assert type(with_pq.quant_method) is method_cls
+                    for i, (sid, n) in enumerate(shards):
+                        c = case(n, k, (8, 8, 1), 300 + i)
+                        c["codebooks"] = (c["codebooks"].float() / k ** 0.5).half()
+                        load_both(with_pq, with_aqlm, c, sid)
+                    same_layer(with_pq, with_aqlm, f"{type(with_pq).__name__} rank {rank}/{world}")
+                    x = torch.randn(7, k_in, generator=gen).half()
+                    with torch.no_grad():
+                        y, _ = with_pq(x.clone())
+                        y_ref, _ = with_aqlm(x.clone())
+                    assert torch.equal(y.view(torch.int16), y_ref.view(torch.int16))
+    finally:
+        R.set_all_reduce(None)
