@@ -182,7 +182,58 @@ class PQLinearMethodBody:
             layer.codes_padded = padded
         elif hasattr(layer, "codes_padded"):
             del layer.codes_padded
+        self._pad_k(layer)
         self._repack_nibbles(layer)
+
+    @staticmethod
+    def _k_padded_groups(g: int, m: int, d: int, elem_bytes: int) -> int:
+        """Smallest G' >= G whose K' = G' * d is whole 64-wide k blocks (what the mma.sync and tcgen05
+        kernels tile K by) and whose code row G' * M * elem_bytes is a multiple of 16 bytes."""
+        gp = g
+        while (gp * d) % 64 or (gp * m * elem_bytes) % 16:
+            gp += 1
+        return gp
+
+    @classmethod
+    def _pad_k(cls, layer: torch.nn.Module, force: bool = False) -> None:
+        """K that is not a multiple of 64 - Llama-2-7B down_proj at TP = 8: K = 1376 - is outside the
+        mma.sync and tcgen05 kernels, which leaves the scalar gather GEMV for every batch above the
+        table GEMV's eight tokens.  ``layer.codes_kpad`` [N, G', M] is the code tensor with zero codes
+        appended up to K' = G' * d; ``_gemm_checkpoint`` feeds it an x zero-padded to K', so the extra
+        groups add  <codeword[0], 0> = 0  exactly and the kernels see an ordinary K' problem.  For 8-bit
+        codes this is the SAME storage as ``codes_padded`` (a view) whenever the two pitches agree."""
+        if hasattr(layer, "codes_kpad"):
+            del layer.codes_kpad
+        codes = layer.codes.data
+        n, g, m = codes.shape
+        d = layer.codebooks.shape[3]
+        if (g * d) % 64 == 0 or not (codes.is_cuda or force) or codes.element_size() > 2:
+            return
+        gp = cls._k_padded_groups(g, m, d, codes.element_size())
+        padded = getattr(layer, "codes_padded", None)
+        if padded is not None and padded.shape[1] == gp * m:
+            layer.codes_kpad = padded.view(n, gp, m)
+        else:
+            kpad = torch.zeros((n, gp, m), dtype=codes.dtype, device=codes.device)
+            kpad[:, :g] = codes
+            layer.codes_kpad = kpad
+
+    def _gemm_checkpoint(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor],
+                         silu_mul: bool = False) -> torch.Tensor:
+        """``pq::gemm`` (or ``pq::gemm_silu_mul``) over the checkpoint tensors - every token count and
+        format, the C side picks the kernel - or, where ``_pad_k`` built one, over the K-padded copy."""
+        codebooks = layer.codebooks
+        parts = list(getattr(codebooks, "output_partition_sizes", []))
+        kpad = getattr(layer, "codes_kpad", None)
+        if kpad is not None:
+            if silu_mul:
+                x = ops.silu_and_mul(x)
+            k_pad = kpad.shape[1] * codebooks.shape[3]
+            x = torch.nn.functional.pad(x, (0, k_pad - x.shape[-1]))
+            return ops.pq_gemm(x, kpad, codebooks, layer.scales, parts, bias)
+        if silu_mul:
+            return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales, parts, bias)
+        return ops.pq_gemm(x, layer.codes, codebooks, layer.scales, parts, bias)
 
     @staticmethod
     def _repack_nibbles(layer: torch.nn.Module) -> None:
@@ -252,8 +303,7 @@ class PQLinearMethodBody:
                                      codes_padded=padded if nibble is None else None)[0]
         # One op for every token count and format: the C side picks GEMV (decode) or the
         # tcgen05 GEMM (prefill). Reference dispatch for comparison: aqlm.py:344-374.
-        return ops.pq_gemm(x, layer.codes, codebooks, layer.scales,
-                           list(output_partition_sizes), bias)
+        return self._gemm_checkpoint(layer, x, bias)
 
     def apply_silu_mul(self, layer: torch.nn.Module, x: torch.Tensor,
                        bias: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -266,7 +316,7 @@ class PQLinearMethodBody:
             dc, dcb = self._decode_tensors(layer)
             return ops.pq_gemm_fused(x, dc, dcb, layer.scales, parts, bias, silu_mul=True,
                                      codes_padded=padded if nibble is None else None)[0]
-        return ops.pq_gemm_silu_mul(x, layer.codes, codebooks, layer.scales, parts, bias)
+        return self._gemm_checkpoint(layer, x, bias, silu_mul=True)
 
     def apply_fused(self, layer: torch.nn.Module, x: torch.Tensor, bias: Optional[torch.Tensor] = None, *,
                     residual: Optional[torch.Tensor] = None, norm=None, allreduce: bool = False,
@@ -298,7 +348,7 @@ class PQLinearMethodBody:
                                        silu_mul=silu_mul, want_ssq=want_ssq,
                                        codes_padded=getattr(layer, "codes_padded", None) if dc is codes else None)
             return y, (ssq if want_ssq else None)
-        y = (ops.pq_gemm_silu_mul if silu_mul else ops.pq_gemm)(x, codes, codebooks, layer.scales, parts, bias)
+        y = self._gemm_checkpoint(layer, x, bias, silu_mul=silu_mul)
         if allreduce:
             y = D.tensor_model_parallel_all_reduce(y)
         if residual is not None:
