@@ -76,6 +76,10 @@ def test_k_padded_copy_and_routing(cpu_ops, fmt):
     res = torch.randn(12, 256, generator=torch.Generator().manual_seed(2)).half()
     out, _, ssq = lin(c["x"], residual=res, want_ssq=True)
     assert torch.equal(out, y_plain + res) and ssq.shape == (12, 1)
+    # eight tokens or fewer keep the checkpoint layout (the decode kernels serve it)
+    del cpu_ops[:]
+    lin(c["x"][:8])
+    assert cpu_ops == [("gemm", (8, k), (256, g, m))]
     # dequantize and the parameters are untouched
     assert dict(lin.named_parameters()).keys() == {"codes", "codebooks", "scales", "bias"}
     # a second call of the hook drops what no longer applies

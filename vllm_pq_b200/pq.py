@@ -198,7 +198,7 @@ class PQLinearMethodBody:
     def _pad_k(cls, layer: torch.nn.Module, force: bool = False) -> None:
         """K that is not a multiple of 64 - Llama-2-7B down_proj at TP = 8: K = 1376 - is outside the
         mma.sync and tcgen05 kernels, which leaves the scalar gather GEMV for every batch above the
-        table GEMV's eight tokens.  ``layer.codes_kpad`` [N, G', M] is the code tensor with zero codes
+        table GEMV's eight tokens (the only batches this copy is used for).  ``layer.codes_kpad`` [N, G', M] is the code tensor with zero codes
         appended up to K' = G' * d; ``_gemm_checkpoint`` feeds it an x zero-padded to K', so the extra
         groups add  <codeword[0], 0> = 0  exactly and the kernels see an ordinary K' problem.  For 8-bit
         codes this is the SAME storage as ``codes_padded`` (a view) whenever the two pitches agree."""
@@ -225,7 +225,9 @@ class PQLinearMethodBody:
         codebooks = layer.codebooks
         parts = list(getattr(codebooks, "output_partition_sizes", []))
         kpad = getattr(layer, "codes_kpad", None)
-        if kpad is not None:
+        # above the table GEMV's eight tokens only: at decode the checkpoint layout already has its kernels
+        # (the table GEMV's cp.async / padded-pitch loaders, the gather GEMV)
+        if kpad is not None and x.numel() // max(x.shape[-1], 1) > 8:
             if silu_mul:
                 x = ops.silu_and_mul(x)
             k_pad = kpad.shape[1] * codebooks.shape[3]
