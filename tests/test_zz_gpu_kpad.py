@@ -1,9 +1,8 @@
 """K-padded private copy on the device (Llama-2-7B down_proj at TP = 8: K = 1376), through the layer API.
 
-Collected last on purpose: this path was added after the round's GPU budget was spent, so its first run
-on a B200 is the round-end one; the kernels it reaches (mma.sync, tcgen05, gather GEMV at K' = 1408) and
-their parity at such shapes are covered by the earlier files.  The host logic is covered on the CPU in
-tests/test_kpad_cpu.py."""
+The kernels it reaches (mma.sync, tcgen05 at K' = 1408; the decode kernels over the checkpoint layout at
+1..8 tokens) are covered at other shapes by the earlier files; the host logic is covered on the CPU in
+tests/test_kpad_cpu.py.  Collected last: it was the last path added in round 2."""
 import pytest
 import torch
 
