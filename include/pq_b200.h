@@ -54,7 +54,8 @@ enum {
   PQ_ERR_WORKSPACE = -5,   /* workspace too small (see pq_b200_workspace_bytes) */
   PQ_ERR_NULL = -6,        /* required pointer is NULL */
   PQ_ERR_UNSUPPORTED = -7, /* valid request this build has no kernel for */
-  PQ_ERR_DEVICE = -8       /* not an sm_100 device */
+  PQ_ERR_DEVICE = -8,      /* not an sm_100 device */
+  PQ_ERR_STATIC_SCRATCH = -9 /* pq_b200_gemv_static: the problem needs more than PQ_STATIC_SCRATCH_BYTES */
 };
 
 /* which kernel family pq_b200_gemm uses */
@@ -202,6 +203,25 @@ PQ_API int64_t pq_b200_gemm_fused_slots(int64_t t, int64_t n, int64_t k, int d, 
 PQ_API int pq_b200_fused_add_rms_norm(void* input, int64_t input_stride, void* residual, int64_t residual_stride,
                                       const void* weight, float eps, int64_t t, int64_t hidden, int dtype,
                                       void* stream);
+
+/* The table GEMV (PQ_ALGO_GEMV_LUT_TMA, 1..8 tokens, nbits <= 8) for callers that cannot allocate and have
+ * no workspace to hand over (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same
+ * arguments and result as pq_b200_gemm(..., PQ_ALGO_GEMV_LUT_TMA, workspace, PQ_STATIC_SCRATCH_BYTES, ...)
+ * minus the workspace: the K-group partial sums and ticket counters live in a file-scope
+ * `static __device__` array of PQ_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the
+ * library holds it until exit).  The call allocates nothing - no cudaMalloc / cudaFree, no allocating
+ * library routine; its only extra work is one cudaMemsetAsync of the 64 KiB ticket area on `stream`.
+ *   * a problem whose pq_b200_workspace_bytes(PQ_ALGO_GEMV_LUT_TMA, ...) exceeds PQ_STATIC_SCRATCH_BYTES
+ *     (t * n above ~124 K outputs) is rejected with PQ_ERR_STATIC_SCRATCH, nothing is launched;
+ *   * every call on a device shares the one array, which keeps the previous call's contents: two calls
+ *     that OVERLAP on the GPU (different streams, or graphs replayed concurrently) race on it - order
+ *     them on one stream or with events. */
+#define PQ_STATIC_SCRATCH_BYTES (4 << 20)
+PQ_API int pq_b200_gemv_static(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                               const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                               int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                               int n_parts, int dtype, void* stream);
 
 /* 1 if kernel family `algo` covers this problem, else 0 (PQ_ALGO_AUTO: always 1). */
 PQ_API int pq_b200_algo_supported(int algo, int64_t t, int64_t n, int64_t k, int d, int nbits, int m);

@@ -220,3 +220,25 @@ def test_round2_entry_points_reject_bad_arguments_without_gpu():
     assert two(16, 16, 64, 0, ptrs, ptrs, ptrs, 2, 2, 1 << 20, None) == -3            # rank out of range
     assert two(16, 16, 60, 0, ptrs, ptrs, ptrs, 0, 2, 1 << 20, None) == -4            # not a multiple of 16 bytes
     assert two(16, 16, 1 << 20, 0, ptrs, ptrs, ptrs, 0, 2, 1 << 20, None) == -5       # larger than the buffers
+
+
+def test_static_scratch_entry_point_rejects_without_gpu():
+    """pq_b200_gemv_static (no reference counterpart): argument errors and the size limit are decided on the
+    host, before any CUDA call."""
+    lib = _lib.load()
+    parts, n_parts = _lib.parts_array([4096])
+    ok = (16, 4096, 16, 16, 16, None, 16, 4096)
+    assert lib.pq_b200_gemv_static(*ok, 1, 4096, 4096, 8, 8, 1, parts, n_parts, 7, None) == -1        # dtype
+    assert lib.pq_b200_gemv_static(*ok, 1, 4096, 4096, 8, 17, 1, parts, n_parts, 0, None) == -2       # format
+    assert lib.pq_b200_gemv_static(*ok, 1, 4096, 4095, 8, 8, 1, parts, n_parts, 0, None) == -3        # k % d
+    assert lib.pq_b200_gemv_static(None, 4096, 16, 16, 16, None, 16, 4096, 1, 4096, 4096, 8, 8, 1, parts, n_parts, 0, None) == -6
+    assert lib.pq_b200_gemv_static(16, 4096, 16, 24, 16, None, 16, 4096, 1, 4096, 4096, 8, 8, 1, parts, n_parts, 0, None) == -4
+    assert lib.pq_b200_gemv_static(*ok, 9, 4096, 4096, 8, 8, 1, parts, n_parts, 0, None) == -7        # 9 tokens
+    assert lib.pq_b200_gemv_static(*ok, 1, 4096, 4096, 8, 16, 1, parts, n_parts, 0, None) == -7       # 16-bit codes
+    big, n_big = _lib.parts_array([28672, 28672])
+    assert lib.pq_b200_workspace_bytes(_lib.ALGO_GEMV_LUT_TMA, 8, 57344, 8192, 8, 8, 1, 2) > (4 << 20)
+    rc = lib.pq_b200_gemv_static(16, 8192, 16, 16, 16, None, 16, 57344, 8, 57344, 8192, 8, 8, 1, big, n_big, 0, None)
+    assert rc == -9 and b"PQ_STATIC_SCRATCH_BYTES" in lib.pq_b200_strerror(rc)
+    import re
+    header = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "pq_b200.h")).read()
+    assert re.search(r"#define PQ_STATIC_SCRATCH_BYTES \(4 << 20\)", header)

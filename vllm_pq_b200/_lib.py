@@ -55,6 +55,9 @@ SIGNATURES = {
     "pq_b200_gemm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                              c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
                              c_int, c_int, c_void_p, c_int64, c_void_p]),
+    "pq_b200_gemv_static": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
+                                    c_int, c_void_p]),
     "pq_b200_gemm_silu_mul": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                       c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_int, _I64P, c_int,
                                       c_int, c_int, c_void_p, c_int64, c_void_p]),

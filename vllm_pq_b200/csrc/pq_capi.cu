@@ -80,6 +80,9 @@ const char* pq_b200_strerror(int code) {
     case PQ_ERR_NULL: return "required pointer is NULL";
     case PQ_ERR_UNSUPPORTED: return "no kernel for this request";
     case PQ_ERR_DEVICE: return "device is not sm_100";
+    case PQ_ERR_STATIC_SCRATCH:
+      return "problem needs more scratch than the static array of pq_b200_gemv_static holds "
+             "(PQ_STATIC_SCRATCH_BYTES); use pq_b200_gemm with a caller workspace";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
   }
 }
@@ -354,3 +357,51 @@ int pq_b200_allreduce_twostage(const void* in, void* out, int64_t n_elems, int d
 }
 
 }  // extern "C"
+
+// ---- pq_b200_gemv_static: the table GEMV with its scratch in a static device array ------------------
+// No counterpart in the reference (include/pq_b200.h).  The array's NAME is a host-side stand-in in host
+// code, not a device address: the address is resolved once per device, with that device current, by
+// cudaGetSymbolAddress, and only that pointer is handed to the dispatcher / kernel.
+static __device__ __align__(256) unsigned char g_static_scratch[PQ_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_ptr(void** out) {
+  static void* ptrs[64] = {};                       // per device ordinal; a benign race writes the same value
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return PQ_ERR_DEVICE;
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return PQ_ERR_DEVICE;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return PQ_OK;
+}
+
+extern "C" int pq_b200_gemv_static(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
+                                   const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
+                                   int64_t n, int64_t k, int d, int nbits, int m, const int64_t* part_sizes,
+                                   int n_parts, int dtype, void* stream) {
+  int rc = check_format(n, k, d, nbits, m, part_sizes, n_parts, dtype);
+  if (rc) return rc;
+  if (!x || !codes || !codebooks || !scales || !y) return PQ_ERR_NULL;
+  if (t <= 0 || t > INT32_MAX || x_stride < k || y_stride < n) return PQ_ERR_SHAPE;
+  if (((uintptr_t)codebooks) & 15) return PQ_ERR_ALIGN;
+  if (!pq::gemv_lut2_supported(t, n, k, d, nbits, m)) return PQ_ERR_UNSUPPORTED;
+  if (pq::gemv_lut2_workspace(t, n, k, d, nbits, m, n_parts) > (int64_t)PQ_STATIC_SCRATCH_BYTES)
+    return PQ_ERR_STATIC_SCRATCH;
+  void* scratch = nullptr;
+  rc = static_scratch_ptr(&scratch);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // the ticket counters at the head of the scratch must start at zero, and the array keeps whatever the
+  // last call (possibly an aborted or a racing one) left there; the partial sums need no clearing
+  cudaError_t e = cudaMemsetAsync(scratch, 0, 64 * 1024, s);
+  if (e != cudaSuccess) return (int)e;
+  return pq::gemv_lut2_dispatch(x, x_stride, codes, codebooks, scales, bias, y, y_stride, t, n, k, d, nbits, m,
+                                part_sizes, n_parts, dtype, scratch, (int64_t)PQ_STATIC_SCRATCH_BYTES, s, 0,
+                                nullptr);
+}
