@@ -35,3 +35,14 @@ def test_reference_arm_other_ranks_exit_without_work():
     lines = run_bench("--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0",
                       env={"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"})
     assert lines == []
+
+
+def test_our_arm_has_no_cpu_fallback():
+    e = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        e.pop(k, None)
+    e["CUDA_VISIBLE_DEVICES"] = ""
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1", "--no-cpu",
+                          "--no-extras"], cwd=ROOT, env=e, capture_output=True, text=True, timeout=600)
+    assert out.returncode != 0 and "no CPU fallback" in out.stderr
+    assert not [ln for ln in out.stdout.splitlines() if ln.startswith("{")]
