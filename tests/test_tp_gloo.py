@@ -241,6 +241,12 @@ def _worker_fused(rank: int, world: int, port: int, ret):
         w_full = O.dequantize_partitions(emb_full["codes"], emb_full["codebooks"], [vocab], emb_full["scales"])
         assert torch.equal(got, w_full[ids])
 
+        # set-up decisions are group-wide: one rank's failure turns the feature off everywhere
+        from vllm_pq_b200 import distributed as D
+        assert D._agree(True, dist.group.WORLD) is True
+        assert D._agree(rank == 0, dist.group.WORLD) is False
+        assert D.fused_allreduce_comm() is None and not D.oneshot_enabled()       # gloo: no peer-memory kernels
+
         # checkpoint walk at world size 2: this rank's vocabulary rows and experts are placed, the other
         # rank's experts are consumed without being reported (mixtral_quant.py:436-439)
         from tests.test_loader_cpu import TinyMoEModel, moe_checkpoint

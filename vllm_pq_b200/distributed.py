@@ -82,7 +82,8 @@ def _setup_oneshot(group: dist.ProcessGroup, max_bytes: int) -> Optional["OneSho
 
 
 def _agree(ok: bool, group: dist.ProcessGroup) -> bool:
-    flag = torch.tensor([1 if ok else 0], device="cuda", dtype=torch.int32)
+    device = "cuda" if dist.get_backend(group) == "nccl" else "cpu"       # gloo: the CPU tests
+    flag = torch.tensor([1 if ok else 0], device=device, dtype=torch.int32)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
     return bool(flag.item())
 
