@@ -154,3 +154,31 @@ def test_layer_restatements_match_live_reference():
         assert G.same_bits(z, z_ref) and int(_ulps(out, out_ref).max()) <= 2
         gu = torch.randn(3, 512, generator=g).to(dtype)
         assert G.same_bits(O.silu_and_mul(gu), SiluAndMul().forward_native(gu))
+
+
+# ---- random formats and shapes: the restatement against the live reference ----------------------------
+from hypothesis import given, settings
+from hypothesis import strategies as st
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="/root/reference not present (GPU box)")
+@settings(max_examples=40, deadline=None, derandomize=True)
+@given(b=st.integers(1, 16), d=st.sampled_from([1, 2, 4, 8, 16, 24]), m=st.integers(1, 6),
+       parts=st.lists(st.integers(1, 24), min_size=1, max_size=4), groups=st.integers(1, 12),
+       t=st.integers(1, 5), bias=st.booleans(), seed=st.integers(0, 1000))
+def test_oracle_matches_live_reference_on_random_formats(b, d, m, parts, groups, t, bias, seed):
+    """Any (nbits, d, M), any partition list, ragged K: dequantised weights (unscaled and scaled) and the
+    generic GEMM carry the bits the reference's functions return (fp16: its only dtype, aqlm.py:238-239)."""
+    ref = ref_loader.load_reference_aqlm()
+    c = O.make_case(parts, groups * d, b, d, m, t=t, dtype=torch.float16, seed=seed, bias=bias, positive_scales=False)
+    assert ref.get_int_dtype(b) == O.get_int_dtype(b) == c["codes"].dtype
+    off = 0
+    for p, n_p in enumerate(parts):
+        cu = ref.unpack_int_data(c["codes"][off:off + n_p], b)
+        assert torch.equal(cu, O.unpack_int_data(c["codes"][off:off + n_p], b))
+        for s in (None, c["scales"][off:off + n_p]):
+            assert G.same_bits(ref.dequantize_weight(cu, c["codebooks"][p * m:(p + 1) * m], s),
+                               O.dequantize_weight(cu, c["codebooks"][p * m:(p + 1) * m], s))
+        off += n_p
+    assert G.same_bits(ref.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"]),
+                       O.generic_dequantize_gemm(c["x"], c["codes"], c["codebooks"], c["scales"], parts, c["bias"]))
