@@ -149,7 +149,8 @@ def load_reference_linear():
     ``parameter.py``, ``model_executor/utils.py``, ``quantization/base_config.py`` and
     ``quantization/aqlm.py`` executed unmodified under stubs.  Returns a namespace with
     ``linear``, ``aqlm``, ``vocab`` (layers/vocab_parallel_embedding.py) and ``mixtral``
-    (models/mixtral_quant.py), ``registry`` (quantization/__init__.py) and ``base_config`` - the module
+    (models/mixtral_quant.py), ``llama`` (models/llama.py), ``registry`` (quantization/__init__.py) and
+    ``base_config`` - the module
     objects - and ``set_tp(rank, world)``: the stubbed
     ``vllm.distributed`` answers with that simulated rank, so every rank's sharded ``create_weights`` and
     ``weight_loader`` can be run in ONE process.  The collectives are not stubbed with arithmetic: the
@@ -214,6 +215,7 @@ def load_reference_linear():
         vocab = _exec("vllm.model_executor.layers.vocab_parallel_embedding",
                       os.path.join(me, "layers/vocab_parallel_embedding.py"))
         mixtral = _exec_mixtral_quant(me, dist, state)
+        llama = _exec_llama(me)
     finally:
         for k in [k for k in sys.modules if k == "vllm" or k.startswith("vllm.")]:
             del sys.modules[k]
@@ -226,7 +228,7 @@ def load_reference_linear():
         """What the stubbed tensor_model_parallel_all_reduce does from now on (None: raise)."""
         state["all_reduce"] = fn
 
-    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, vocab=vocab, mixtral=mixtral, registry=registry,
+    _cached_linear = types.SimpleNamespace(linear=linear, aqlm=aqlm, vocab=vocab, mixtral=mixtral, llama=llama, registry=registry,
                                            base_config=sys_base, set_tp=set_tp,
                                            set_all_reduce=set_all_reduce)
     return _cached_linear
@@ -271,3 +273,47 @@ def _exec_mixtral_quant(me: str, dist, state):
     sys.modules["vllm.model_executor.layers.quantization"].QuantizationConfig = base.QuantizationConfig
     _exec("vllm.model_executor.layers.layernorm", os.path.join(me, "layers/layernorm.py"))
     return _exec("vllm.model_executor.models.mixtral_quant", os.path.join(me, "models/mixtral_quant.py"))
+
+
+def _functions_of(path: str, names, namespace: dict):
+    """Compile single top-level functions of a reference file (unmodified source, cut out by the AST) into
+    ``namespace`` - for helper functions of modules whose other imports cannot be satisfied here."""
+    import ast
+    with open(path) as fh:
+        tree = ast.parse(fh.read(), filename=path)
+    body = [node for node in tree.body if isinstance(node, ast.FunctionDef) and node.name in names]
+    assert {node.name for node in body} == set(names), (path, names)
+    exec(compile(ast.Module(body=body, type_ignores=[]), path, "exec"), namespace)
+    return [namespace[n] for n in names]
+
+
+def _exec_llama(me: str):
+    """models/llama.py for ``LlamaModel.load_weights`` (llama.py:369-433), the weight walk an AQLM Llama
+    checkpoint goes through.  Called inside load_reference_linear()'s stub environment, after
+    _exec_mixtral_quant() has put the placeholder modules in place.  ``default_weight_loader`` and
+    ``maybe_remap_kv_scale_name`` are the reference's own functions, cut out of
+    model_loader/weight_utils.py (that module's other imports - hub, safetensors, config - are not
+    available under the stubs)."""
+    import logging
+    from typing import Optional
+    comp = _AnyModule("vllm.compilation")
+    dec = _AnyModule("vllm.compilation.decorators")
+    dec.support_torch_compile = lambda cls: cls
+    sys.modules["vllm.compilation"], sys.modules["vllm.compilation.decorators"] = comp, dec
+    log = logging.getLogger("vllm.reference_stub")
+    log.warning_once = log.warning
+    ns = {"torch": torch, "Optional": Optional, "logger": log}
+    loader, remap = _functions_of(os.path.join(me, "model_loader/weight_utils.py"),
+                                  ["default_weight_loader", "maybe_remap_kv_scale_name"], ns)
+    wu = sys.modules["vllm.model_executor.model_loader.weight_utils"]
+    wu.default_weight_loader, wu.maybe_remap_kv_scale_name = loader, remap
+    utils = sys.modules["vllm.model_executor.models.utils"]
+    utils.is_pp_missing_parameter = lambda name, model: False          # no pipeline parallelism here
+    class LazyDict(dict):                              # vllm/utils.py: values are factories
+        def __getitem__(self, key):
+            return super().__getitem__(key)()
+
+    sys.modules["vllm.utils"] = _AnyModule("vllm.utils")
+    sys.modules["vllm.utils"].LazyDict = LazyDict
+    _exec("vllm.model_executor.layers.activation", os.path.join(me, "layers/activation.py"))
+    return _exec("vllm.model_executor.models.llama", os.path.join(me, "models/llama.py"))

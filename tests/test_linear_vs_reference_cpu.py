@@ -444,3 +444,56 @@ def test_pq_method_plugs_into_the_reference_tree(tp, monkeypatch):
                     assert torch.equal(y.view(torch.int16), y_ref.view(torch.int16))
     finally:
         R.set_all_reduce(None)
+
+
+# ---- the checkpoint walk against the reference's own LlamaModel.load_weights -----------
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("fmt", [(8, 8, 1), (8, 8, 2), (16, 8, 1)], ids=["8x8x1", "8x8x2", "16x8x1"])
+def test_loader_places_what_the_reference_load_weights_places(tp, tmp_path, fmt, world):
+    """loader.load_pq_linears on our stack against LlamaModel.load_weights (llama.py:369-433, run unmodified as
+    a plain function) on a module tree of the reference's own layers with its AQLM method: the same
+    checkpoint tensors, every simulated rank, the same set of loaded parameters and the same bits."""
+    from tests.test_loader_cpu import SHAPE, make_checkpoint
+    from vllm_pq_b200 import loader as L
+    from vllm_pq_b200 import stack as S
+    R, set_tp = tp
+    b, d, m = fmt
+    make_checkpoint(str(tmp_path), fmt)
+    weights = list(L.safetensors_weights_iterator(str(tmp_path)))
+    hd = SHAPE.head_dim
+
+    class Block(torch.nn.Module):
+        pass
+
+    for rank in range(world):
+        set_tp(rank, world)
+        ours = S.PQLlamaLinearStack(SHAPE, P.PQConfig(d, b, m, 1), torch.float16)
+        loaded, skipped = L.load_pq_linears(ours, weights)
+        rcfg = R.aqlm.AQLMConfig(d, b, m, 1)
+        kw = dict(bias=False, params_dtype=torch.float16, quant_config=rcfg)
+        tree = Block()
+        tree.quant_config = rcfg
+        tree.layers = torch.nn.ModuleList()
+        for _ in range(SHAPE.layers):
+            layer, layer.self_attn, layer.mlp = Block(), Block(), Block()
+            layer.self_attn.qkv_proj = R.linear.QKVParallelLinear(SHAPE.hidden, hd, SHAPE.heads, SHAPE.kv_heads, **kw)
+            layer.self_attn.o_proj = R.linear.RowParallelLinear(SHAPE.heads * hd, SHAPE.hidden, **kw)
+            layer.mlp.gate_up_proj = R.linear.MergedColumnParallelLinear(SHAPE.hidden, [SHAPE.intermediate] * 2, **kw)
+            layer.mlp.down_proj = R.linear.RowParallelLinear(SHAPE.intermediate, SHAPE.hidden, **kw)
+            tree.layers.append(layer)
+        fill_garbage(tree, 7)
+        # what LlamaForCausalLM hands LlamaModel.load_weights: the "model." prefix stripped (AutoWeightsLoader);
+        # only the tensors of modules this tree has (no norms / embeddings here - ours reports those as skipped)
+        pq_names = {n for n, _ in weights if n not in skipped}
+        ref_loaded = R.llama.LlamaModel.load_weights(
+            tree, ((n[len("model."):], t) for n, t in weights if n in pq_names or "rotary_emb" in n))
+        strip = lambda n: n.replace(".self_attn.", ".").replace(".mlp.", ".")          # noqa: E731
+        assert {strip(n) for n in ref_loaded} == loaded
+        assert all("rotary_emb" in s or "layernorm" in s or "embed_tokens" in s or "lm_head" in s for s in skipped)
+        mine, ref = dict(ours.named_parameters()), dict(tree.named_parameters())
+        assert {strip(n) for n in ref} == set(mine)
+        for name, p in ref.items():
+            q = mine[strip(name)]
+            assert q.shape == p.shape and q.dtype == p.dtype, name
+            assert torch.equal(q.data.view(torch.int16) if q.dtype.is_floating_point else q.data,
+                               p.data.view(torch.int16) if p.dtype.is_floating_point else p.data), f"{name} rank {rank}/{world}"
