@@ -497,3 +497,55 @@ def test_loader_places_what_the_reference_load_weights_places(tp, tmp_path, fmt,
             assert q.shape == p.shape and q.dtype == p.dtype, name
             assert torch.equal(q.data.view(torch.int16) if q.dtype.is_floating_point else q.data,
                                p.data.view(torch.int16) if p.dtype.is_floating_point else p.data), f"{name} rank {rank}/{world}"
+
+
+# ---- the MLP with the activation on down_proj's input against the reference's LlamaMLP ----
+@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("bias", [False, True])
+def test_mlp_with_input_activation_matches_reference_llama_mlp(tp, monkeypatch, world, bias):
+    """LlamaMLP.forward (llama.py:89-93): gate_up_proj -> SiluAndMul -> down_proj, the reference's own class on
+    the CPU (generic format).  Ours: ``down_proj(gate_up, input_act="silu_and_mul")``, the activation taken by
+    ``pq::gemm_silu_mul`` - here the oracle's SiLU*mul (bit-equal to the reference's, test_oracle_golden.py)
+    followed by its generic_dequantize_gemm.  Every simulated rank's partial result, bit for bit."""
+    from vllm_pq_b200 import _custom_ops as ops
+    R, set_tp = tp
+    fmt = (8, 8, 1)
+    b, d, m = fmt
+
+    def cpu_gemm(x, codes, codebooks, scales, parts, bias, algo=0):
+        return O.generic_dequantize_gemm(x, codes, codebooks, scales, parts, bias)
+
+    monkeypatch.setattr(ops, "pq_gemm", cpu_gemm)
+    monkeypatch.setattr(ops, "pq_gemm_silu_mul", lambda x, *a, **k: cpu_gemm(O.silu_and_mul(x), *a, **k))
+    import vllm_pq_b200.linear as lin_mod
+    monkeypatch.setattr(lin_mod, "tensor_model_parallel_all_reduce", lambda t: t)
+    monkeypatch.setattr(D, "tensor_model_parallel_all_reduce", lambda t: t)
+    R.set_all_reduce(lambda t: t)
+    gen = torch.Generator().manual_seed(21)
+    gate, up, down = case(FFN, HIDDEN, fmt, 401), case(FFN, HIDDEN, fmt, 402), case(HIDDEN, FFN, fmt, 403)
+    for c, k in ((gate, HIDDEN), (up, HIDDEN), (down, FFN)):
+        c["codebooks"] = (c["codebooks"].float() / k ** 0.5).half()
+    try:
+        for rank in range(world):
+            set_tp(rank, world)
+            torch.set_default_dtype(torch.float16)
+            try:
+                theirs = R.llama.LlamaMLP(HIDDEN, FFN, "silu", quant_config=R.aqlm.AQLMConfig(d, b, m, 1), bias=bias)
+            finally:
+                torch.set_default_dtype(torch.float32)
+            kw = dict(bias=bias, params_dtype=torch.float16, quant_config=P.PQConfig(d, b, m, 1))
+            gu, dn = P.MergedColumnParallelLinear(HIDDEN, [FFN, FFN], **kw), P.RowParallelLinear(FFN, HIDDEN, **kw)
+            pick = (lambda c: c) if bias else (lambda c: {k_: v for k_, v in c.items() if k_ != "bias"})
+            load_both(gu, theirs.gate_up_proj, pick(gate), 0)
+            load_both(gu, theirs.gate_up_proj, pick(up), 1)
+            load_both(dn, theirs.down_proj, pick(down))
+            x = torch.randn(5, HIDDEN, generator=gen).half()
+            with torch.no_grad():
+                y_ref = theirs(x.clone())
+                h, _ = gu(x.clone())
+                y, _ = dn(h, input_act="silu_and_mul")
+                y_sep, _ = dn(O.silu_and_mul(h))                  # the activation as its own step: same bits
+            assert torch.equal(y.view(torch.int16), y_ref.view(torch.int16)), f"rank {rank}/{world}"
+            assert torch.equal(y_sep.view(torch.int16), y_ref.view(torch.int16))
+    finally:
+        R.set_all_reduce(None)
