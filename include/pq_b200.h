@@ -216,7 +216,10 @@ PQ_API int pq_b200_fused_add_rms_norm(void* input, int64_t input_stride, void* r
  *     (t * n above ~124 K outputs) is rejected with PQ_ERR_STATIC_SCRATCH, nothing is launched;
  *   * every call on a device shares the one array, which keeps the previous call's contents: two calls
  *     that OVERLAP on the GPU (different streams, or graphs replayed concurrently) race on it - order
- *     them on one stream or with events. */
+ *     them on one stream or with events;
+ *   * the array's address is resolved on the first call on each device (cudaGetSymbolAddress, with that
+ *     device current): make that first call eagerly, before capturing a graph - like every kernel of this
+ *     library, whose first launch sets function attributes. */
 #define PQ_STATIC_SCRATCH_BYTES (4 << 20)
 PQ_API int pq_b200_gemv_static(const void* x, int64_t x_stride, const void* codes, const void* codebooks,
                                const void* scales, const void* bias, void* y, int64_t y_stride, int64_t t,
